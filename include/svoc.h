@@ -1,0 +1,130 @@
+/* svoc.h — C ABI of libsvoc: batched two-pass robust oracle consensus on B200 (sm_100a).
+ *
+ * The reference (Ophiase/Stochastic-Vector-Oracle-Consensus) has no FFI layer: the
+ * consensus update is reached through a Cairo contract ABI, a few notebook functions
+ * and a few client helpers.  Each entry point below names the reference interface it
+ * replaces (paths relative to the reference checkout).  A "round" is one full update
+ * with all N oracle vectors present, i.e. what contract/src/contract.cairo:442-503
+ * (constrained) / :370-434 (unconstrained) compute once every oracle has committed.
+ *
+ * Conventions
+ *   - device entry points take DEVICE pointers and a cudaStream_t passed as void*;
+ *     `_host` entry points take HOST pointers and do their own staging;
+ *   - predictions are row-major [T][N][D]  (trial, oracle, dimension);
+ *   - optional outputs may be NULL;
+ *   - return value 0 = ok, negative = bad argument / CUDA error (text via
+ *     svoc_last_error()); per-round data errors (the contract's panics) go to
+ *     status[T], never to the return code;
+ *   - no CPU fallback exists: without a CUDA device every compute call fails.
+ */
+#ifndef SVOC_H
+#define SVOC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVOC_VERSION 100
+
+/* element types of the prediction tensor */
+#define SVOC_I32 0
+#define SVOC_I64 1
+#define SVOC_F32 2
+#define SVOC_F64 3
+
+/* centre estimators */
+#define SVOC_CENTRE_SMOOTH_MEDIAN_CAIRO 0 /* contract/src/math.cairo:113-126 (3-value branch is dead code) */
+#define SVOC_CENTRE_MEDIAN 1              /* np.median, ipynb beta :355, client/oracle_scheduler.py:108 */
+#define SVOC_CENTRE_MEAN 2                /* math.cairo:256-269; gaussian_algorithm_demo.ipynb:191-204 */
+#define SVOC_CENTRE_DEFAULT (-1)          /* second pass: same as first when constrained, MEAN otherwise */
+
+/* which of two oracles with EQUAL divergence stays reliable at the cut */
+#define SVOC_TIE_HIGH_INDEX_KEPT 0 /* contract/src/sort.cairo:96-102: order (value asc, index desc) */
+#define SVOC_TIE_LOW_INDEX_KEPT 1  /* stable argsort, ipynb beta :342-367 */
+
+/* per-round status = first panic in the contract's evaluation order */
+#define SVOC_ST_OK 0
+#define SVOC_ST_INTERVAL_INPUT 1    /* math.cairo:298-310 via contract.cairo:591-593 */
+#define SVOC_ST_SQRT_REL1 2         /* math.cairo:271-292: sqrt(1) divides by zero */
+#define SVOC_ST_MAX_SPREAD_ZERO 3   /* contract.cairo:365-368 */
+#define SVOC_ST_REL1_RANGE 4        /* math.cairo:294-296 after contract.cairo:467 / :397 */
+#define SVOC_ST_SECOND_PASS_SHAPE 5 /* fewer than 2 (constrained) / 1 reliable rows */
+#define SVOC_ST_SQRT_REL2 6
+#define SVOC_ST_REL2_RANGE 7        /* contract.cairo:488 / :419 */
+#define SVOC_ST_SKEW_PANIC 8        /* math.cairo:320-338: variance in {0,1} or R <= 2 */
+#define SVOC_ST_KURT_PANIC 9        /* math.cairo:340-363: R <= 3 */
+#define SVOC_ST_OVERFLOW 10         /* i128 overflow in the contract */
+#define SVOC_ST_FIRST_PASS_SHAPE 11 /* N < 2 */
+#define SVOC_ST_ENGINE_RANGE 12     /* |x| > 2^30 (unconstrained): beyond this engine's 64-bit fast path */
+
+typedef struct svoc_config {
+    int32_t n_oracles;        /* N  — constructor `oracles.len()`, contract.cairo:236-246 */
+    int32_t dimension;        /* D  — constructor `dimension` */
+    int32_t n_failing;        /* F  — constructor `n_failing_oracles`; R = N - F rows stay reliable */
+    int32_t constrained;      /* constructor `constrained` */
+    int64_t max_spread_wsad;  /* constructor `unconstrained_max_spread` (fixed form, 1e6-scaled) */
+    double max_spread;        /* same, float form */
+    int32_t centre;           /* SVOC_CENTRE_* for the first pass */
+    int32_t centre2;          /* SVOC_CENTRE_* for the second pass or SVOC_CENTRE_DEFAULT */
+    int32_t tie_rule;         /* SVOC_TIE_* */
+    int32_t dtype;            /* SVOC_I32/I64 (fixed form) or SVOC_F32/F64 (float form) */
+    int32_t want_moments;     /* also compute skewness / kurtosis (contract.cairo:491-500) */
+    int32_t reserved;
+} svoc_config;
+
+/* Output block shared by the device entry points.  Element type of the value outputs:
+ * int64 for the fixed form; the input type (float / double) for the float form.
+ * All pointers except consensus, rel1, rel2 and status may be NULL. */
+typedef struct svoc_outputs {
+    void *essence1;     /* [T][D] first-pass essence        — essence_first_pass, contract.cairo:459 */
+    void *qr;           /* [T][N] per-oracle quadratic risk — quadratic_risk_values, contract.cairo:463 */
+    void *rel1;         /* [T]    get_first_pass_consensus_reliability(), contract.cairo:633-636 */
+    uint32_t *reliable; /* [T][ceil(N/32)] bit i of word i/32 = oracle i reliable — OracleInfo.reliable */
+    void *consensus;    /* [T][D] get_consensus_value(), contract.cairo:619-631 */
+    void *rel2;         /* [T]    get_second_pass_consensus_reliability(), contract.cairo:638-641 */
+    void *skew;         /* [T][D] get_skewness(), contract.cairo:643-655 */
+    void *kurt;         /* [T][D] get_kurtosis() */
+    int32_t *status;    /* [T]    SVOC_ST_* */
+} svoc_outputs;
+
+/* Fixed-point ("wsad", value * 1e6 as signed integer) form — bit-exact restatement of
+ * update_constrained_consensus / update_unconstrained_consensus
+ * (contract/src/contract.cairo:442-503 / :370-434) with math.cairo, sort.cairo and
+ * signed_decimal.cairo underneath.  cfg->dtype is SVOC_I32 or SVOC_I64. */
+int svoc_consensus_fixed(const svoc_config *cfg, const void *pred, int64_t n_rounds,
+                         const svoc_outputs *out, void *stream);
+
+/* Floating-point form: the notebook estimator (identify_failing_oracles +
+ * restricted_median, ipynb beta :354-371; predictions_to_eel_values,
+ * client/oracle_scheduler.py:106-111) and the contract evaluated in real arithmetic.
+ * cfg->dtype is SVOC_F32 or SVOC_F64. */
+int svoc_consensus_float(const svoc_config *cfg, const void *pred, int64_t n_rounds,
+                         const svoc_outputs *out, void *stream);
+
+/* Same two calls with HOST buffers: predictions are staged to the device in chunks on
+ * internal streams and the outputs copied back; the call returns when the outputs are
+ * complete.  This is the call a client holding numpy arrays makes
+ * (client/contract.py:200-208 `update_all_the_predictions` is its on-chain analogue). */
+int svoc_consensus_fixed_host(const svoc_config *cfg, const void *pred, int64_t n_rounds,
+                              const svoc_outputs *out);
+int svoc_consensus_float_host(const svoc_config *cfg, const void *pred, int64_t n_rounds,
+                              const svoc_outputs *out);
+
+/* 1 - 2*mean(|A - median(A)|) over each flattened [N*D] array — `expected_reliability`,
+ * ipynb beta :260-267.  pred is [T][n_values] float64 on the device; out is [T] float64. */
+int svoc_expected_reliability(const double *pred, int64_t n_arrays, int32_t n_values, double *out,
+                              void *stream);
+
+const char *svoc_last_error(void);
+int svoc_version(void);
+/* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */
+int64_t svoc_launch_count(void);
+/* name of the kernel variant the dispatcher picks for (cfg): "small<NPAD>" or "generic" */
+const char *svoc_kernel_variant(const svoc_config *cfg);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVOC_H */

@@ -1,0 +1,7 @@
+// consensus_f32.cu — instantiates the consensus kernels for one element type
+// (kept in its own translation unit so the variants compile in parallel).
+#include "consensus_kernel.cuh"
+
+namespace svoc {
+int consensus_f32(const Params &p, const Plan &pl, cudaStream_t st) { return dispatch_npad<FloatTr<float>>(p, pl, st); }
+}  // namespace svoc

@@ -1,0 +1,7 @@
+// consensus_i64.cu — instantiates the consensus kernels for one element type
+// (kept in its own translation unit so the variants compile in parallel).
+#include "consensus_kernel.cuh"
+
+namespace svoc {
+int consensus_i64(const Params &p, const Plan &pl, cudaStream_t st) { return dispatch_npad<FixedTr<i64>>(p, pl, st); }
+}  // namespace svoc

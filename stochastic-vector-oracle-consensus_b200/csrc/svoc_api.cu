@@ -1,0 +1,154 @@
+// svoc_api.cu — host side of libsvoc: argument checks, launch planning and the C ABI
+// declared in include/svoc.h.
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "consensus_kernel.cuh"
+
+namespace svoc {
+
+// ------------------------------------------------------------------------------ host side
+static thread_local std::string g_err;
+static int64_t g_launches = 0;
+static std::mutex g_mu;
+
+int fail(const std::string &m) {
+    g_err = m;
+    return -1;
+}
+
+static int npad_for(int N) { return N <= 8 ? 8 : N <= 16 ? 16 : N <= 32 ? 32 : N <= 64 ? 64 : 0; }
+
+static size_t elem_size(int dtype) { return (dtype == SVOC_I32 || dtype == SVOC_F32) ? 4 : 8; }
+
+static size_t smem_bytes(const svoc_config &c, int rb, int tile_smem) {
+    const size_t es = elem_size(c.dtype);
+    const size_t vs = (c.dtype == SVOC_F32) ? 4 : 8;  // val_t / acc_t size
+    auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+    size_t s = 0;
+    if (tile_smem) s += al((size_t)rb * c.n_oracles * c.dimension * es);
+    s += al((size_t)rb * c.dimension * vs);
+    s += al((size_t)rb * c.n_oracles * vs);
+    s += al((size_t)rb * sizeof(int));
+    s += 16;
+    s += al((size_t)rb * c.n_oracles);
+    return s;
+}
+
+static Plan make_plan(const svoc_config &c) {
+    Plan pl;
+    pl.npad = npad_for(c.n_oracles);
+    pl.threads = pl.npad ? 128 : 256;
+    const size_t budget = pl.npad ? 40 * 1024 : 200 * 1024;
+    int rb = pl.threads / (c.dimension > 0 ? c.dimension : 1);
+    if (rb < 1) rb = 1;
+    while (rb > 1 && smem_bytes(c, rb, 1) > budget) rb >>= 1;
+    pl.tile_smem = smem_bytes(c, rb, 1) <= 200 * 1024 ? 1 : 0;
+    pl.rb = rb;
+    pl.smem = smem_bytes(c, rb, pl.tile_smem);
+    return pl;
+}
+
+static int validate(const svoc_config *cfg, const void *pred, int64_t T, const svoc_outputs *out, bool fixed) {
+    if (!cfg || !out) return fail("null config or outputs");
+    if (T < 0) return fail("negative round count");
+    if (T > 0 && !pred) return fail("null predictions");
+    if (cfg->n_oracles < 1 || cfg->dimension < 1) return fail("n_oracles and dimension must be >= 1");
+    if (cfg->n_oracles > 65535) return fail("n_oracles > 65535 is not supported");
+    if (cfg->n_failing < 0) return fail("n_failing must be >= 0");
+    if (fixed && !(cfg->dtype == SVOC_I32 || cfg->dtype == SVOC_I64)) return fail("fixed form needs dtype I32 or I64");
+    if (!fixed && !(cfg->dtype == SVOC_F32 || cfg->dtype == SVOC_F64)) return fail("float form needs dtype F32 or F64");
+    if (!fixed && (cfg->n_oracles < 2 || cfg->n_failing >= cfg->n_oracles))
+        return fail("float form needs n_oracles >= 2 and n_failing < n_oracles");
+    if (cfg->centre < 0 || cfg->centre > 2) return fail("bad centre");
+    if (cfg->centre2 < -1 || cfg->centre2 > 2) return fail("bad centre2");
+    if (cfg->tie_rule < 0 || cfg->tie_rule > 1) return fail("bad tie_rule");
+    if (!out->consensus || !out->rel1 || !out->rel2 || !out->status)
+        return fail("consensus, rel1, rel2 and status outputs are required");
+    return 0;
+}
+
+static Params make_params(const svoc_config &c, const void *pred, int64_t T, const svoc_outputs &o, const Plan &pl) {
+    Params p;
+    p.pred = pred;
+    p.T = T;
+    p.N = c.n_oracles;
+    p.D = c.dimension;
+    p.F = c.n_failing;
+    p.R = c.n_oracles - c.n_failing;
+    p.constrained = c.constrained ? 1 : 0;
+    p.ms_w = c.max_spread_wsad;
+    p.ms_f = c.max_spread;
+    p.centre = c.centre;
+    p.centre2 = c.centre2 == SVOC_CENTRE_DEFAULT ? (c.constrained ? c.centre : SVOC_CENTRE_MEAN) : c.centre2;
+    p.tie = c.tie_rule;
+    p.want_moments = c.want_moments ? 1 : 0;
+    p.essence1 = o.essence1;
+    p.qr = o.qr;
+    p.rel1 = o.rel1;
+    p.reliable = o.reliable;
+    p.consensus = o.consensus;
+    p.rel2 = o.rel2;
+    p.skew = o.skew;
+    p.kurt = o.kurt;
+    p.status = o.status;
+    p.rb = pl.rb;
+    p.words = (c.n_oracles + 31) / 32;
+    p.tile_smem = pl.tile_smem;
+    return p;
+}
+
+int consensus_device(const svoc_config *cfg, const void *pred, int64_t T, const svoc_outputs *out, void *stream,
+                     bool fixed) {
+    if (int rc = validate(cfg, pred, T, out, fixed)) return rc;
+    if (T == 0) return 0;
+    const Plan pl = make_plan(*cfg);
+    const Params p = make_params(*cfg, pred, T, *out, pl);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (cfg->dtype) {
+        case SVOC_I32: return consensus_i32(p, pl, st);
+        case SVOC_I64: return consensus_i64(p, pl, st);
+        case SVOC_F32: return consensus_f32(p, pl, st);
+        default: return consensus_f64(p, pl, st);
+    }
+}
+
+void set_error(const std::string &m) { g_err = m; }
+void count_launch() {
+    std::lock_guard<std::mutex> lk(g_mu);
+    ++g_launches;
+}
+
+}  // namespace svoc
+
+// ------------------------------------------------------------------------------ C ABI
+extern "C" {
+
+int svoc_consensus_fixed(const svoc_config *cfg, const void *pred, int64_t n_rounds, const svoc_outputs *out,
+                         void *stream) {
+    return svoc::consensus_device(cfg, pred, n_rounds, out, stream, true);
+}
+
+int svoc_consensus_float(const svoc_config *cfg, const void *pred, int64_t n_rounds, const svoc_outputs *out,
+                         void *stream) {
+    return svoc::consensus_device(cfg, pred, n_rounds, out, stream, false);
+}
+
+const char *svoc_last_error(void) { return svoc::g_err.c_str(); }
+int svoc_version(void) { return SVOC_VERSION; }
+int64_t svoc_launch_count(void) {
+    std::lock_guard<std::mutex> lk(svoc::g_mu);
+    return svoc::g_launches;
+}
+const char *svoc_kernel_variant(const svoc_config *cfg) {
+    static thread_local char buf[32];
+    if (!cfg) return "invalid";
+    const int np = svoc::npad_for(cfg->n_oracles);
+    if (np) snprintf(buf, sizeof buf, "small%d", np);
+    else snprintf(buf, sizeof buf, "generic");
+    return buf;
+}
+
+}  // extern "C"

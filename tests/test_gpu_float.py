@@ -1,0 +1,131 @@
+"""GPU parity, float form: libsvoc vs the reference notebook's own outputs (golden fixtures)
+and vs the float64 CPU oracle.  Tolerances: 1e-6 relative in fp64, 1e-4 in fp32 (north star)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import ranks_equal_up_to_ties, seed_of
+
+pytestmark = pytest.mark.gpu
+
+RTOL = {torch.float64: 1e-6, torch.float32: 1e-4}
+
+
+def _np(r):
+    d = {k: (getattr(r, k).cpu().numpy() if getattr(r, k) is not None else None)
+         for k in ("consensus", "rel1", "rel2", "status", "essence1", "qr", "skew", "kurt")}
+    d["reliable"] = r.reliable.cpu().numpy()
+    return d
+
+
+def test_notebook_golden(golden):
+    """identify_failing_oracles + restricted_median of the reference, on its own seeded draws."""
+    import svoc
+    for (n, d, f, t) in golden["shapes"]:
+        key = f"n{n}_d{d}_f{f}"
+        pred = golden[key + "_pred"]
+        for dt in (torch.float64, torch.float32):
+            x = torch.from_numpy(pred).to(dt).cuda()
+            r = _np(svoc.consensus_float(x, int(f), centre=svoc.CENTRE_MEDIAN, tie_rule=svoc.TIE_LOW_INDEX_KEPT))
+            # the reference's mask: exact wherever the cut is not a rounding-level near-tie
+            qs = np.sort(r["qr"].astype(np.float64), axis=1)
+            gap = (qs[:, n - f] - qs[:, n - f - 1]) / np.maximum(qs[:, n - f], 1e-30)
+            safe = gap > 10 * RTOL[dt]
+            assert safe.mean() > 0.75
+            assert np.array_equal(r["reliable"][safe], golden[key + "_mask"][safe]), key
+            np.testing.assert_allclose(r["consensus"][safe], golden[key + "_consensus"][safe], rtol=RTOL[dt], atol=1e-7)
+            # rank_array (ipynb :342-352): rank 0 = largest deviation
+            ranks = (n - 1) - np.argsort(np.argsort(r["qr"], axis=1, kind="stable"), axis=1, kind="stable")
+            if dt == torch.float64:
+                for k in range(int(t)):
+                    # compare up to (near-)ties: sqrt in the reference can merge or split 1-ulp neighbours
+                    dev = np.round(np.sqrt(r["qr"][k]), 12)
+                    assert ranks_equal_up_to_ties(ranks[k], golden[key + "_ranks"][k], dev), (key, k)
+
+
+def test_expected_reliability_kats(golden):
+    """The two printed known answers of the notebook (cells 14-15): 0.762 and 0.807."""
+    import svoc
+    for k in ("kat1d", "kat2d"):
+        a = torch.from_numpy(golden[k + "_wsad"] * 1e-6).reshape(1, -1).cuda()
+        v = float(svoc.expected_reliability(a)[0])
+        assert f"{v:0.3f}" == f"{float(golden[k + '_printed']):0.3f}"
+        assert abs(v - float(golden[k + "_expected_reliability"])) < 1e-12
+    for (n, d, f, t) in golden["shapes"]:
+        key = f"n{n}_d{d}_f{f}"
+        a = torch.from_numpy(golden[key + "_pred"]).cuda()
+        v = svoc.expected_reliability(a).cpu().numpy()
+        np.testing.assert_allclose(v, golden[key + "_expected_reliability"], rtol=1e-12, atol=1e-12)
+
+
+SHAPES = [(7, 2, 2), (7, 6, 2), (7, 1, 2), (20, 2, 4), (32, 8, 6), (33, 5, 6), (64, 16, 12), (100, 3, 20), (256, 128, 51)]
+
+
+@pytest.mark.parametrize("N,D,F", SHAPES)
+@pytest.mark.parametrize("dt", [torch.float64, torch.float32])
+@pytest.mark.parametrize("mode", ["contract", "unconstrained", "notebook", "mean"])
+def test_float_vs_oracle(N, D, F, dt, mode):
+    import svoc
+    from oracle import cref
+    rng = np.random.default_rng(seed_of(N, D, F, mode))
+    T = 300 if N * D <= 1024 else (30 if N * D <= 8192 else 4)
+    if mode == "unconstrained":
+        x = rng.normal(20.0, 3.0, (T, N, D))
+    else:
+        x = rng.beta(10, 15, (T, N, D))
+        bad = rng.random((T, N)) < 0.2
+        x = np.where(bad[:, :, None], rng.random((T, N, D)), x)
+    x = x.astype(np.float32).astype(np.float64)   # identical inputs for both precisions
+    kw = {"contract": dict(constrained=True, centre=0, tie=0),
+          "unconstrained": dict(constrained=False, max_spread=10.0, centre=0, tie=0),
+          "notebook": dict(constrained=True, centre=1, tie=1),
+          "mean": dict(constrained=True, centre=2, tie=0)}[mode]
+    ora = cref.float_batch(x, F, want_moments=True, nthreads=0, **kw)
+    r = _np(svoc.consensus_float(torch.from_numpy(x).to(dt).cuda(), F, constrained=kw["constrained"],
+                                 max_spread=kw.get("max_spread", 0.0), centre=kw["centre"], tie_rule=kw["tie"],
+                                 want_moments=True))
+    rt = RTOL[dt]
+    np.testing.assert_allclose(r["essence1"], ora["essence1"], rtol=rt, atol=1e-7)
+    np.testing.assert_allclose(r["qr"], ora["qr"], rtol=10 * rt, atol=1e-9)
+    np.testing.assert_allclose(r["rel1"], ora["rel1"], rtol=rt, atol=10 * rt)
+    qs = np.sort(ora["qr"], axis=1)
+    safe = (qs[:, N - F] - qs[:, N - F - 1]) > 20 * rt * qs[:, N - F]   # cut not within rounding of a tie
+    assert safe.mean() > 0.75
+    assert np.array_equal(r["reliable"][safe], ora["reliable"][safe])
+    np.testing.assert_allclose(r["consensus"][safe], ora["consensus"][safe], rtol=rt, atol=1e-7)
+    np.testing.assert_allclose(r["rel2"][safe], ora["rel2"][safe], rtol=rt, atol=10 * rt)
+    mt = 1e-6 if dt == torch.float64 else 2e-2   # z-scores amplify fp32 rounding
+    np.testing.assert_allclose(r["skew"][safe], ora["skew"][safe], rtol=mt, atol=mt)
+    np.testing.assert_allclose(r["kurt"][safe], ora["kurt"][safe], rtol=mt, atol=10 * mt)
+
+
+def test_ties_follow_the_rule():
+    """Identical rows (colluders) tie exactly; the contract keeps the higher index, numpy the lower."""
+    import svoc
+    x = np.array([[[0.5, 0.5], [0.4, 0.4], [0.6, 0.6], [0.4, 0.4], [0.6, 0.6], [0.5, 0.5], [0.9, 0.1]]])
+    t = torch.from_numpy(x).cuda()
+    hi = svoc.consensus_float(t, 2, tie_rule=svoc.TIE_HIGH_INDEX_KEPT).reliable[0].tolist()
+    lo = svoc.consensus_float(t, 2, tie_rule=svoc.TIE_LOW_INDEX_KEPT).reliable[0].tolist()
+    # essence (0.5, 0.45): rows 2 and 4 tie for the second-largest qr; row 6 is the largest.
+    assert hi == [True, True, False, True, True, True, False]
+    assert lo == [True, True, True, True, False, True, False]
+
+
+def test_full_size_properties_c4():
+    """BASELINE config 4 shape (N=256, D=128, fp32, colluders): translation equivariance of the
+    consensus, invariance of qr, and exact reliable count, on a batch far larger than the oracle runs."""
+    import svoc
+    g = torch.Generator(device="cuda").manual_seed(9)
+    T, N, D, F = 2048, 256, 128, 51
+    x = torch.rand((T, N, D), generator=g, device="cuda") * 0.25 + 0.25
+    x[:, :F, :] = x[:, :1, :] + 0.125            # F colluders share one vector
+    r = svoc.consensus_float(x, F)
+    assert torch.all(r.reliable.sum(dim=1) == N - F)
+    assert torch.all(~r.reliable[:, :F])          # the colluders are the outliers here
+    shift = 0.25                                  # exact in binary: results must shift exactly
+    r2 = svoc.consensus_float(x + shift, F)
+    assert torch.equal(r.reliable_words, r2.reliable_words)
+    torch.testing.assert_close(r2.consensus, r.consensus + shift, rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(r2.qr, r.qr, rtol=1e-4, atol=1e-7)
+    kept = x[:, F:, :]
+    torch.testing.assert_close(r.consensus, 0.5 * (kept.sort(dim=1).values[:, (N - F) // 2 - 1] + kept.sort(dim=1).values[:, (N - F) // 2]))
