@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py — consensus rounds/s of the fused consensus kernel on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5m] [--impl reference]
+
+One "step" = one pass of the consensus hot path over one batch of synthetic predictions.
+Default workload = BASELINE.json config 4 (1M rounds, n=256, d=128, fp32, colluders): the
+configuration the north star's roofline target is quoted on.  Prints ONE JSON line.
+
+  value     rounds/s with the batch resident in HBM (device entry point, CUDA-event timed)
+  e2e       rounds/s through the C-ABI *_host entry point: pinned host buffers in, host
+            outputs back, H2D/D2H inside the timed region
+  roofline  algorithmic bytes per launch / mean launch time vs the measured HBM copy peak
+  cpu_baseline  oracle/svoc_ref.c (C port of the reference) on the box's host cores, bounded sample
+
+`--impl reference` times the CPU port alone (the reference itself is Cairo + a notebook and
+cannot run on the box), with all host threads, and prints the same line with impl=reference.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "stochastic-vector-oracle-consensus_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+WORKLOADS = {
+    # name: rounds, N, D, F, dtype, form, description
+    "c2": dict(T=1_000_000, N=7, D=2, F=2, dtype="f32", desc="1M rounds n=7 d=2 F=2 fp32 (BASELINE config 2)"),
+    "c3": dict(T=10_000_000, N=64, D=16, F=12, dtype="i32", desc="10M rounds n=64 d=16 F=12 fixed-point int32 (BASELINE config 3)"),
+    "c4": dict(T=1_000_000, N=256, D=128, F=51, dtype="f32", desc="1M rounds n=256 d=128 F=51 fp32, colluding oracles (BASELINE config 4)"),
+    "c5m": dict(T=16_777_216, N=32, D=8, F=6, dtype="f32", desc="2^24 materialised rounds n=32 d=8 F=6 fp32 (BASELINE config 5 shape)"),
+}
+
+
+def algorithmic_bytes_per_round(N, D, s_in, s_out):
+    """every input byte once + consensus + rel1 + rel2 + mask words + status."""
+    return N * D * s_in + D * s_out + 2 * s_out + 4 * ((N + 31) // 32) + 4
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop, self.th = index, [], threading.Event(), None
+
+    def _loop(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.th = threading.Thread(target=self._loop, daemon=True)
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_predictions(torch, wl, T, device, seed):
+    """Synthetic predictions of the named shape on the device: honest oracles ~ beta(10, 15) per component,
+    F failing ones uniform (c2/c3/c5m) or colluding on one shared vector mode+0.15 (c4), at random positions."""
+    import svoc
+    N, D, F = wl["N"], wl["D"], wl["F"]
+    colluding = wl is WORKLOADS["c4"]
+    dt = {"f32": torch.float32, "i32": torch.int32}[wl["dtype"]]
+    return svoc.generate(T, N, D, F, a=10.0, b=15.0, failing="colluding" if colluding else "uniform",
+                         shift=0.15, seed=seed, dtype=dt, device=device).pred
+
+
+def run_consensus(svoc, wl, x, host=False):
+    fixed = wl["dtype"] == "i32"
+    if fixed:
+        f = svoc.consensus_fixed_host if host else svoc.consensus_fixed
+        return f(x, wl["F"], want_moments=False, want_qr=False, want_essence=False)
+    f = svoc.consensus_float_host if host else svoc.consensus_float
+    return f(x, wl["F"], want_moments=False, want_qr=False, want_essence=False)
+
+
+def cpu_port(wl, seconds=10.0, nthreads=0):
+    """Time oracle/svoc_ref.c (all host threads unless told otherwise) on a bounded sample of the workload."""
+    import numpy as np
+    from oracle import cref
+    cref.build()
+    N, D, F = wl["N"], wl["D"], wl["F"]
+    cores = cref.max_threads() if nthreads <= 0 else nthreads
+    rng = np.random.default_rng(0)
+
+    def batch(T):
+        x = rng.beta(10, 15, (T, N, D))
+        x[:, :F, :] = rng.random((T, F, D))
+        return x
+
+    def run(x):
+        t0 = time.perf_counter()
+        if wl["dtype"] == "i32":
+            cref.fixed_batch((x * 1e6).astype(np.int64), F, True, 0, False, nthreads=nthreads)
+        else:
+            cref.float_batch(x, F, want_moments=False, nthreads=nthreads)
+        return time.perf_counter() - t0
+
+    T = max(cores * 4, 64)
+    dt = run(batch(T))                               # calibration
+    T = int(max(T, min(T * seconds / max(dt, 1e-6), 4e8 / (N * D))))
+    x = batch(T)
+    dt = run(x)
+    return {"value": T / dt, "unit": "rounds/s", "cores": cores, "kind": "port",
+            "sample": f"{T} rounds of {N}x{D} (F={F}, {'wsad int64' if wl['dtype'] == 'i32' else 'float64'}) through "
+                      f"oracle/svoc_ref.c, {cores} pthreads, {dt:.2f} s"}, T, dt
+
+
+def numpy_restatement_rate(wl, seconds=2.0):
+    """The reference's float path as it actually runs: single CPython thread + numpy (oracle/float_oracle.py)."""
+    import numpy as np
+    from oracle import float_oracle as flo
+    rng = np.random.default_rng(1)
+    x = rng.beta(10, 15, (4096, wl["N"], wl["D"]))
+    n, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < seconds and n < x.shape[0]:
+        m = flo.identify_failing_oracles(x[n], wl["F"])
+        flo.restricted_median(x[n], m)
+        n += 1
+    return n / (time.perf_counter() - t0)
+
+
+def reference_arm(args, wl, rank):
+    if rank != 0:
+        return
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    rates = []
+    base = None
+    for i in range(args.warmup + args.steps):
+        base, T, dt = cpu_port(wl, seconds=per_step)
+        if i >= args.warmup:
+            rates.append((T, dt))
+    total_T = sum(t for t, _ in rates)
+    total_dt = sum(d for _, d in rates)
+    v = total_T / total_dt
+    base["value"] = v
+    line = {"impl": "reference", "metric": "consensus rounds/sec", "value": v, "unit": "rounds/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_dt / max(1, len(rates)),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if wl["dtype"] != "i32" else "int64", "data": "synthetic",
+            "config": {"workload": wl["desc"], "n_oracles": wl["N"], "dimension": wl["D"], "n_failing": wl["F"],
+                       "note": "CPU port of the reference (oracle/svoc_ref.c): the reference itself is Cairo + a notebook and cannot run here"},
+            "cpu_baseline": base,
+            "e2e": {"value": v, "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="svoc", choices=["svoc", "reference"])
+    ap.add_argument("--rounds", type=int, default=0, help="override rounds per GPU per step (parity/debug only)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary workloads")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        reference_arm(args, wl, rank)
+        return
+
+    import torch
+    import svoc
+    svoc._lib.load()  # fail loudly when the CUDA library is missing
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    N, D, F = wl["N"], wl["D"], wl["F"]
+    s_in = 4
+    s_out = 8 if wl["dtype"] == "i32" else 4
+    T = args.rounds or wl["T"]
+    free, _total = torch.cuda.mem_get_info()
+    need = T * (N * D * s_in + (D + 2) * s_out + 4 * ((N + 31) // 32) + 4)
+    shrunk = False
+    while need > 0.90 * free:
+        T //= 2
+        need //= 2
+        shrunk = True
+    x = make_predictions(torch, wl, T, dev, seed=1234 + rank)
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    stats = svoc.RunningStats(N, device=dev)
+
+    def step():
+        r = run_consensus(svoc, wl, x)
+        stats.update(r)
+        if dist is not None:
+            stats.allreduce()
+        return r
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    l0 = svoc.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 2)]
+    kern_ms = []
+    with ClockSampler(local) as clk:
+        ev[0].record()
+        for i in range(args.steps):
+            ev[2 * i + 1].record()
+            r = run_consensus(svoc, wl, x)
+            ev[2 * i + 2].record()
+            stats.update(r)
+            if dist is not None:
+                stats.allreduce()
+        ev[-1].record()
+        barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    kern_ms = [ev[2 * i + 1].elapsed_time(ev[2 * i + 2]) for i in range(args.steps)]
+    launches = svoc.launch_count() - l0
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t[0])
+    value = world * T * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host buffers through the C-ABI *_host entry point (bounded sample of the same workload)
+    e2e_T = int(min(T, max(4096, (4 << 30) // (N * D * s_in))))
+    xh = torch.empty((e2e_T, N, D), dtype=x.dtype, pin_memory=True)
+    xh.copy_(x[:e2e_T])
+    torch.cuda.synchronize()
+    run_consensus(svoc, wl, xh, host=True)
+    barrier()
+    e2e_steps = max(2, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        rh = run_consensus(svoc, wl, xh, host=True)
+    barrier()
+    e2e_dt = time.perf_counter() - t0
+    t = torch.tensor([e2e_dt], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * e2e_T * e2e_steps / float(t[0])
+    d2h = sum(v.numel() * v.element_size() for v in (rh.consensus, rh.rel1, rh.rel2, rh.status, rh.reliable_words))
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    B = algorithmic_bytes_per_round(N, D, s_in, s_out)
+    peak, peak_src = measured_peak()
+    kms = statistics.mean(kern_ms)
+    achieved = T * B / (kms * 1e-3) / 1e9
+    line = {
+        "metric": "consensus rounds/sec", "value": value, "unit": "rounds/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32" if wl["dtype"] == "f32" else "int64 (int32 storage)", "data": "synthetic",
+        "config": {"workload": wl["desc"], "n_oracles": N, "dimension": D, "n_failing": F, "rounds_per_gpu_per_step": T,
+                   "rounds_shrunk_to_fit_hbm": shrunk, "kernel_variant": svoc.kernel_variant(N, D, x.dtype),
+                   "l2": "inputs per step (%.1f GB) far exceed L2; no flush needed" % (T * N * D * s_in / 1e9)
+                   if T * N * D * s_in > 1e9 else "inputs fit in L2: reported as rounds/s only, HBM fraction not meaningful",
+                   "per_step": "consensus kernel + stats accumulation" + (" + NCCL allreduce of the stats buffer" if world > 1 else "")},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "bytes_per_round": B, "kernel_ms": kms},
+        "e2e": {"value": e2e_value, "unit": "rounds/s", "h2d_bytes_per_step": e2e_T * N * D * s_in,
+                "d2h_bytes_per_step": d2h, "sample_rounds_per_step": e2e_T, "steps": e2e_steps,
+                "api": "svoc.consensus_%s_host -> svoc_consensus_%s_host (C ABI, pinned host buffers)" % (("fixed",) * 2 if wl["dtype"] == "i32" else ("float",) * 2)},
+        "gpu_launches": int(launches),
+        "clocks": clk.summary(),
+        "stats": stats.summary(),
+    }
+    if not args.no_cpu:
+        base, _, _ = cpu_port(wl, seconds=10.0)
+        base["numpy_restatement_single_thread_rounds_per_s"] = numpy_restatement_rate(wl)
+        line["cpu_baseline"] = base
+    if not args.no_secondary and world == 1:
+        del x, xh, r, rh
+        torch.cuda.empty_cache()
+        sec = {}
+        for name in ("c2", "c3", "c5m"):
+            if name == args.workload:
+                continue
+            w2 = WORKLOADS[name]
+            x2 = make_predictions(torch, w2, w2["T"], dev, seed=99)
+            for _ in range(3):
+                run_consensus(svoc, w2, x2)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(3):
+                run_consensus(svoc, w2, x2)
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b) / 3
+            B2 = algorithmic_bytes_per_round(w2["N"], w2["D"], 4, 8 if w2["dtype"] == "i32" else 4)
+            sec[name] = {"workload": w2["desc"], "rounds_per_s": w2["T"] / (ms * 1e-3), "ms_per_step": ms,
+                         "algorithmic_GBps": w2["T"] * B2 / (ms * 1e-3) / 1e9, "frac_of_peak": w2["T"] * B2 / (ms * 1e-3) / 1e9 / peak}
+            del x2
+            torch.cuda.empty_cache()
+        line["secondary_workloads"] = sec
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

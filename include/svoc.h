@@ -117,6 +117,58 @@ int svoc_consensus_float_host(const svoc_config *cfg, const void *pred, int64_t 
 int svoc_expected_reliability(const double *pred, int64_t n_arrays, int32_t n_values, double *out,
                               void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Synthetic workloads — the notebook generators on a counter-based Philox4x32-10 stream:
+ *   generate_beta_oracles / generate_2d_beta_oracles   ipynb beta :37-68
+ *   generate_2d_gaussian_oracles                        gaussian_distribution_for_tests.ipynb:37-52
+ * Honest oracles draw law(a[d], b[d]) per component, the n_failing failing ones are uniform (or
+ * collude on one shared vector), and failing POSITIONS are a uniformly random subset, which is what
+ * the reference's `np.random.shuffle` of [failing..., honest...] yields.  Every draw is a pure
+ * function of (seed, global trial index, oracle, dimension): results do not depend on the launch
+ * geometry or on how trials are sharded over GPUs.  numpy's MT19937 stream is not reproduced;
+ * parity with the reference generators is distributional. */
+#define SVOC_LAW_BETA 0      /* honest ~ beta(a, b); failing ~ uniform(0, 1) */
+#define SVOC_LAW_GAUSSIAN 1  /* honest ~ normal(a = mu, b = sigma); failing ~ uniform(mu, 5 sigma) */
+#define SVOC_FAIL_UNIFORM 0
+#define SVOC_FAIL_COLLUDING 1 /* every failing oracle submits clip(mode + shift) (beta) / mu + shift*sigma (gaussian) */
+#define SVOC_MAX_LAW_PARAMS 8
+
+typedef struct svoc_gen_config {
+    int32_t n_oracles, dimension, n_failing;
+    int32_t law;                  /* SVOC_LAW_* */
+    int32_t failing;              /* SVOC_FAIL_* */
+    int32_t dtype;                /* output type: SVOC_F32/F64, or SVOC_I32/I64 = int(x * 1e6) (to_wsad, ipynb beta :250) */
+    int32_t n_params;             /* 1..SVOC_MAX_LAW_PARAMS; dimension d uses a[d % n_params], b[d % n_params] */
+    int32_t reserved;
+    double a[SVOC_MAX_LAW_PARAMS];
+    double b[SVOC_MAX_LAW_PARAMS];
+    double shift;                 /* colluders' offset */
+    uint64_t seed;
+    int64_t trial_offset;         /* global index of the first trial of this call (multi-GPU sharding) */
+} svoc_gen_config;
+
+/* pred: [T][N][D] of cfg->dtype on the device; honest (may be NULL): [T][ceil(N/32)] bit mask, bit = 1
+ * for honest oracles (the `validity` / `true_oracles` array the notebook generators return). */
+int svoc_generate(const svoc_gen_config *cfg, int64_t n_rounds, void *pred, uint32_t *honest, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Per-oracle divergence accumulators and reliability histograms over many rounds — the inputs
+ * of a replacement decision (contract.cairo:345-363 keeps only the last `reliable` flag; the
+ * admin vote contract.cairo:547-580, 661-738 is left to humans).  All counters live in two
+ * caller-owned device buffers so that several GPUs can combine them with one SUM all-reduce each:
+ *   counts  int64  [SVOC_STATS_COUNTS_BASE + 2*N]
+ *           [0] rounds  [1] rounds with status 0  [2..15] rounds per status code
+ *           [16..271] histogram of rel1, 256 bins over [0,1]   [272..527] histogram of rel2
+ *           [528..528+N) per-oracle count of rounds in which the oracle was NOT reliable
+ *           [528+N..528+2N) per-oracle sum of qr (fixed form: exact wsad integers; float form: unused)
+ *   sums    float64 [SVOC_STATS_SUMS_BASE + N]
+ *           [0] sum rel1  [1] sum rel2  [2] sum rel1^2  [3] sum rel2^2  [4..4+N) per-oracle sum of qr (float form)
+ * Only rounds with status 0 enter the histograms, sums and per-oracle accumulators. */
+#define SVOC_STATS_COUNTS_BASE 528
+#define SVOC_STATS_SUMS_BASE 4
+int svoc_accumulate_stats(const svoc_config *cfg, int64_t n_rounds, const svoc_outputs *out, int64_t *counts,
+                          double *sums, void *stream);
+
 const char *svoc_last_error(void);
 int svoc_version(void);
 /* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */

@@ -44,6 +44,19 @@ class SvocOutputs(C.Structure):
     ]
 
 
+class SvocGenConfig(C.Structure):
+    _fields_ = [
+        ("n_oracles", C.c_int32), ("dimension", C.c_int32), ("n_failing", C.c_int32), ("law", C.c_int32),
+        ("failing", C.c_int32), ("dtype", C.c_int32), ("n_params", C.c_int32), ("reserved", C.c_int32),
+        ("a", C.c_double * 8), ("b", C.c_double * 8), ("shift", C.c_double), ("seed", C.c_uint64),
+        ("trial_offset", C.c_int64),
+    ]
+
+
+LAW_BETA, LAW_GAUSSIAN = 0, 1
+FAIL_UNIFORM, FAIL_COLLUDING = 0, 1
+STATS_COUNTS_BASE, STATS_SUMS_BASE, STATS_HIST_BINS = 528, 4, 256
+
 # every symbol include/svoc.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "svoc_consensus_fixed": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs), C.c_void_p]),
@@ -51,6 +64,8 @@ SYMBOLS = {
     "svoc_consensus_fixed_host": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
     "svoc_consensus_float_host": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
     "svoc_expected_reliability": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "svoc_generate": (C.c_int, [C.POINTER(SvocGenConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "svoc_accumulate_stats": (C.c_int, [C.POINTER(SvocConfig), C.c_int64, C.POINTER(SvocOutputs), C.c_void_p, C.c_void_p, C.c_void_p]),
     "svoc_last_error": (C.c_char_p, []),
     "svoc_version": (C.c_int, []),
     "svoc_launch_count": (C.c_int64, []),

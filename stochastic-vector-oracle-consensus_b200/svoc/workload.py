@@ -1,0 +1,144 @@
+"""Synthetic workloads and running statistics on the device.
+
+`generate` is the on-device counterpart of the notebook generators (generate_beta_oracles /
+generate_2d_beta_oracles, ipynb beta :37-68; generate_2d_gaussian_oracles,
+gaussian_distribution_for_tests.ipynb:37-52).  `RunningStats` keeps the per-oracle divergence
+accumulators and reliability histograms that a replacement decision needs, in two buffers
+that multi-GPU runs combine with one SUM all-reduce each.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from .engine import _DTYPES, ConsensusResult, make_config
+from ._lib import SvocGenConfig, SvocOutputs
+
+
+@dataclass
+class Generated:
+    pred: torch.Tensor           # [T, N, D]
+    honest_words: torch.Tensor   # [T, ceil(N/32)] int32, bit = 1 for honest oracles
+    n_oracles: int
+
+    @property
+    def honest(self) -> torch.Tensor:
+        """[T, N] bool — the `validity` array the notebook generators return."""
+        idx = torch.arange(self.n_oracles, device=self.honest_words.device)
+        return ((self.honest_words[:, idx // 32] >> (idx % 32)) & 1).bool()
+
+
+def _seq(v, n=8):
+    v = list(v) if isinstance(v, (Sequence, torch.Tensor)) and not isinstance(v, str) else [v]
+    if not 1 <= len(v) <= n:
+        raise ValueError("between 1 and 8 law parameters are supported (dimension d uses parameter d % len)")
+    return v
+
+
+def generate(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="beta", failing="uniform", shift=0.15,
+             seed=0, trial_offset=0, dtype=torch.float32, device=None) -> Generated:
+    """Draw `n_rounds` rounds of oracle predictions on the device.
+
+    law="beta": honest ~ beta(a[d], b[d]), failing ~ uniform(0, 1); law="gaussian": honest ~
+    normal(mu=a[d], sigma=b[d]), failing ~ uniform(mu, 5 sigma).  failing="colluding" makes every
+    failing oracle submit the same vector (mode + shift, clipped to [0, 1] for beta).  Integer
+    dtypes store int(x * 1e6) (`to_wsad`).  Failing positions are a random subset per round.
+    """
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if device.type != "cuda":
+        raise ValueError("svoc.generate runs on a CUDA device only")
+    av, bv = _seq(a), _seq(b)
+    if len(av) != len(bv):
+        raise ValueError("a and b need the same length")
+    cfg = SvocGenConfig(n_oracles=int(n_oracles), dimension=int(dimension), n_failing=int(n_failing),
+                        law={"beta": _lib.LAW_BETA, "gaussian": _lib.LAW_GAUSSIAN}[law],
+                        failing={"uniform": _lib.FAIL_UNIFORM, "colluding": _lib.FAIL_COLLUDING}[failing],
+                        dtype=_DTYPES[dtype], n_params=len(av), reserved=0, shift=float(shift),
+                        seed=int(seed) & (2**64 - 1), trial_offset=int(trial_offset))
+    for k, (x, y) in enumerate(zip(av, bv)):
+        cfg.a[k], cfg.b[k] = float(x), float(y)
+    pred = torch.empty((n_rounds, n_oracles, dimension), dtype=dtype, device=device)
+    words = torch.empty((n_rounds, (n_oracles + 31) // 32), dtype=torch.int32, device=device)
+    if n_rounds:
+        with torch.cuda.device(device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(_lib.load().svoc_generate(C.byref(cfg), n_rounds, C.c_void_p(pred.data_ptr()),
+                                                 C.c_void_p(words.data_ptr()), C.c_void_p(st)))
+    return Generated(pred, words, n_oracles)
+
+
+class RunningStats:
+    """Accumulators over many rounds: status counts, rel1/rel2 histograms (256 bins over [0, 1]),
+    per-oracle "not reliable" counts and per-oracle sum of quadratic risk."""
+
+    def __init__(self, n_oracles: int, device=None):
+        self.n = int(n_oracles)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.counts = torch.zeros(_lib.STATS_COUNTS_BASE + 2 * self.n, dtype=torch.int64, device=self.device)
+        self.sums = torch.zeros(_lib.STATS_SUMS_BASE + self.n, dtype=torch.float64, device=self.device)
+        self._reduced = None
+
+    def update(self, res: ConsensusResult) -> None:
+        T = res.status.shape[0]
+        if T == 0:
+            return
+        fixed = res.rel1.dtype == torch.int64
+        dt = _lib.I64 if fixed else _DTYPES[res.rel1.dtype]
+        cfg = make_config(self.n, res.consensus.shape[1], 0, dt)
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+        outs = SvocOutputs(essence1=None, qr=ptr(res.qr), rel1=ptr(res.rel1), reliable=ptr(res.reliable_words),
+                           consensus=ptr(res.consensus), rel2=ptr(res.rel2), skew=None, kurt=None, status=ptr(res.status))
+        with torch.cuda.device(self.device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(_lib.load().svoc_accumulate_stats(C.byref(cfg), T, C.byref(outs), C.c_void_p(self.counts.data_ptr()),
+                                                         C.c_void_p(self.sums.data_ptr()), C.c_void_p(st)))
+
+    def allreduce(self, group=None):
+        """SUM the local accumulators over all ranks (NCCL over NVLink on GPUs); returns (counts, sums)
+        of the whole job and leaves the local accumulators untouched."""
+        import torch.distributed as dist
+        c, s = self.counts.clone(), self.sums.clone()
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(c, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
+        self._reduced = (c, s)
+        return c, s
+
+    def summary(self, reduced: bool = False) -> dict:
+        c, s = self._reduced if (reduced and self._reduced is not None) else (self.counts, self.sums)
+        c, s = c.cpu(), s.cpu()
+        B, H, n = _lib.STATS_COUNTS_BASE, _lib.STATS_HIST_BINS, self.n
+        ok = int(c[1])
+        return {
+            "rounds": int(c[0]), "rounds_ok": ok,
+            "status_counts": {_lib.STATUS_NAMES[k]: int(c[2 + k]) for k in range(13) if int(c[2 + k])},
+            "mean_rel1": float(s[0]) / ok if ok else None, "mean_rel2": float(s[1]) / ok if ok else None,
+            "unreliable_fraction_max": float(c[B:B + n].max()) / ok if ok else None,
+            "unreliable_fraction_min": float(c[B:B + n].min()) / ok if ok else None,
+        }
+
+    def histograms(self, reduced: bool = False):
+        c = (self._reduced[0] if (reduced and self._reduced is not None) else self.counts).cpu()
+        H = _lib.STATS_HIST_BINS
+        return c[16:16 + H].clone(), c[16 + H:16 + 2 * H].clone()
+
+    def unreliable_counts(self) -> torch.Tensor:
+        B = _lib.STATS_COUNTS_BASE
+        return self.counts[B:B + self.n]
+
+    def qr_sums(self, fixed: bool) -> torch.Tensor:
+        B = _lib.STATS_COUNTS_BASE
+        return self.counts[B + self.n:B + 2 * self.n] if fixed else self.sums[_lib.STATS_SUMS_BASE:]
+
+    def replacement_candidates(self, min_fraction: float = 0.5) -> list:
+        """Oracles flagged unreliable in at least `min_fraction` of the accepted rounds — the indices an
+        admin would put in `update_proposition` (contract.cairo:661-717)."""
+        ok = int(self.counts[1])
+        if ok == 0:
+            return []
+        frac = self.unreliable_counts().double() / ok
+        return torch.nonzero(frac >= min_fraction).flatten().tolist()

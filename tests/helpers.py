@@ -78,3 +78,14 @@ def ranks_equal_up_to_ties(r_a, r_b, dev):
         if dev[i] != dev[j]:
             return False
     return True
+
+
+def masks_equal_up_to_cut_ties(mask_a, mask_b, qr, N, F, rtol):
+    """Asserts that two reliable masks differ only on oracles whose qr lies within `rtol` (relative) of the
+    selection cut, and returns the per-round bool vector 'masks identical'."""
+    qs = np.sort(qr, axis=1)
+    cut = 0.5 * (qs[:, N - F - 1] + qs[:, N - F]) if 0 < F < N else qs[:, -1]
+    diff = mask_a != mask_b
+    near = np.abs(qr - cut[:, None]) <= rtol * np.abs(cut[:, None]) + 1e-300
+    assert not np.any(diff & ~near), "reliable masks differ away from the selection cut"
+    return ~diff.any(axis=1)

@@ -1,0 +1,134 @@
+"""GPU: the on-device generators (a27) and the running accumulators."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def test_positions_follow_the_pinned_philox_stream():
+    """Failing positions = the F smallest Philox position keys; checked against the KAT-pinned Python Philox."""
+    import svoc
+    from philox_ref import failing_flags
+    seed, off = 0x1234_5678_9ABC_DEF0, 1_000_000_007
+    g = svoc.generate(64, 7, 2, 2, a=10, b=15, seed=seed, trial_offset=off)
+    honest = g.honest.cpu().numpy()
+    for t in range(64):
+        assert (~honest[t]).tolist() == failing_flags(seed, off + t, 7, 2), t
+    g = svoc.generate(4, 256, 3, 51, seed=seed)
+    honest = g.honest.cpu().numpy()
+    for t in range(4):
+        assert (~honest[t]).tolist() == failing_flags(seed, t, 256, 51)
+
+
+def test_sharding_invariance_and_determinism():
+    import svoc
+    a = svoc.generate(1000, 32, 8, 6, a=[10, 20], b=[15, 30], seed=42)
+    b0 = svoc.generate(400, 32, 8, 6, a=[10, 20], b=[15, 30], seed=42, trial_offset=0)
+    b1 = svoc.generate(600, 32, 8, 6, a=[10, 20], b=[15, 30], seed=42, trial_offset=400)
+    assert torch.equal(a.pred, torch.cat([b0.pred, b1.pred])) and torch.equal(a.honest_words, torch.cat([b0.honest_words, b1.honest_words]))
+    c = svoc.generate(1000, 32, 8, 6, a=[10, 20], b=[15, 30], seed=43)
+    assert not torch.equal(a.pred, c.pred)
+
+
+@pytest.mark.parametrize("a,b", [(10.0, 15.0), (10.0, 30.0), (100.0, 100.0), (2.0, 5.0), (0.5, 0.7)])
+def test_beta_distribution(a, b):
+    import svoc
+    from scipy import stats
+    g = svoc.generate(20000, 20, 2, 4, a=a, b=b, seed=7)
+    x = g.pred.cpu().numpy().astype(np.float64)
+    h = g.honest.cpu().numpy()
+    assert np.all(h.sum(axis=1) == 16)
+    honest, failing = x[h].ravel(), x[~h].ravel()
+    m, v = stats.beta.stats(a, b, moments="mv")
+    assert abs(honest.mean() - m) < 4 * np.sqrt(v / honest.size) + 1e-4
+    assert abs(honest.var() - v) / v < 0.02
+    assert stats.kstest(honest[:20000], stats.beta(a, b).cdf).pvalue > 1e-3
+    assert stats.kstest(failing[:20000], "uniform").pvalue > 1e-3
+    # failing positions are uniform over the oracles (np.random.shuffle in the reference)
+    frac = (~h).mean(axis=0)
+    assert np.all(np.abs(frac - 0.2) < 0.02)
+
+
+def test_gaussian_law_and_colluders_and_wsad():
+    import svoc
+    from scipy import stats
+    g = svoc.generate(5000, 20, 2, 4, a=[20.0, 12.0], b=[3.0, 2.0], law="gaussian", seed=3, dtype=torch.float64)
+    x, h = g.pred.cpu().numpy(), g.honest.cpu().numpy()
+    for d, (mu, sg) in enumerate([(20.0, 3.0), (12.0, 2.0)]):
+        hv = x[..., d][h]
+        assert abs(hv.mean() - mu) < 0.05 and abs(hv.std() - sg) < 0.05
+        assert stats.kstest((hv[:20000] - mu) / sg, "norm").pvalue > 1e-3
+        fv = x[..., d][~h]       # np.random.uniform(mu, 5 sigma), gaussian_distribution_for_tests.ipynb:41-44
+        lo, hi = min(mu, 5 * sg), max(mu, 5 * sg)
+        assert fv.min() >= lo - 1e-6 and fv.max() <= hi + 1e-6
+    c = svoc.generate(100, 16, 4, 5, a=10, b=15, failing="colluding", shift=0.15, seed=1)
+    x, h = c.pred.cpu().numpy(), c.honest.cpu().numpy()
+    mode = (10 - 1) / (10 + 15 - 2)
+    assert np.allclose(x[~h], mode + 0.15, atol=1e-6)
+    # integer outputs are to_wsad(x) = int(x * 1e6) of the same draws
+    f = svoc.generate(500, 7, 2, 2, a=10, b=15, seed=5, dtype=torch.float32).pred
+    i = svoc.generate(500, 7, 2, 2, a=10, b=15, seed=5, dtype=torch.int32).pred
+    assert torch.equal(i, (f * torch.tensor(1e6, dtype=torch.float32, device=f.device)).to(torch.int32))
+    assert int(i.min()) >= 0 and int(i.max()) <= 1_000_000
+
+
+def test_montecarlo_statistics_match_the_reference_benchmark(golden):
+    """benchmark() of the reference (ipynb beta :385-402) re-run at K = 8000..20000 by make_golden.py:
+    identification success and 'true consensus reliability' of the on-device pipeline must agree
+    within Monte-Carlo noise."""
+    import svoc
+    for (n, f, a, k, succ, rel) in golden["benchmark_stats"]:
+        n, f = int(n), int(f)
+        T = 200_000
+        g = svoc.generate(T, n, 1, f, a=a, b=a, seed=int(1000 * n + f + a))
+        r = svoc.consensus_float(g.pred, f, centre=svoc.CENTRE_MEDIAN, tie_rule=svoc.TIE_LOW_INDEX_KEPT, want_qr=False)
+        ident = r.reliable
+        success = (ident == g.honest).all(dim=1).float().mean().item() * 100
+        # truth median: median over the honest rows
+        big = torch.where(g.honest, g.pred[..., 0], torch.full_like(g.pred[..., 0], float("inf")))
+        srt = big.sort(dim=1).values
+        R = n - f
+        truth_med = 0.5 * (srt[:, (R - 1) // 2] + srt[:, R // 2])
+        dist = (r.consensus[:, 0] - truth_med).abs().mean().item()
+        reliability = 100 * (1 - 2 * dist)
+        p = succ / 100
+        tol = 4 * 100 * np.sqrt(max(p * (1 - p), 1e-4) / k) + 0.3
+        assert abs(success - succ) < tol, (n, f, a, success, succ)
+        assert abs(reliability - rel) < 0.35, (n, f, a, reliability, rel)
+
+
+def test_running_stats_match_numpy():
+    import svoc
+    g = svoc.generate(30000, 16, 4, 3, a=10, b=15, seed=11, dtype=torch.int32)
+    x = g.pred.clone()
+    x[::7, 0, 0] = 2_000_000          # some rounds panic with INTERVAL_INPUT
+    r = svoc.consensus_fixed(x, 3, want_moments=True)
+    st = svoc.RunningStats(16)
+    st.update(r)
+    st.update(r)
+    torch.cuda.synchronize()
+    c = st.counts.cpu().numpy()
+    status = r.status.cpu().numpy()
+    ok = status == 0
+    assert c[0] == 2 * len(status) and c[1] == 2 * ok.sum()
+    for code in range(13):
+        assert c[2 + code] == 2 * (status == code).sum()
+    rel1 = r.rel1.cpu().numpy()[ok] * 1e-6
+    rel2 = r.rel2.cpu().numpy()[ok] * 1e-6
+    h1 = np.bincount(np.clip((rel1 * 256).astype(int), 0, 255), minlength=256)
+    h2 = np.bincount(np.clip((rel2 * 256).astype(int), 0, 255), minlength=256)
+    assert np.array_equal(c[16:272], 2 * h1) and np.array_equal(c[272:528], 2 * h2)
+    unrel = (~r.reliable.cpu().numpy())[ok].sum(axis=0)
+    assert np.array_equal(c[528:544], 2 * unrel)
+    qsum = r.qr.cpu().numpy()[ok].sum(axis=0)
+    assert np.array_equal(c[544:560], 2 * qsum)
+    s = st.sums.cpu().numpy()
+    np.testing.assert_allclose(s[0], 2 * rel1.sum(), rtol=1e-12)
+    np.testing.assert_allclose(s[3], 2 * (rel2 ** 2).sum(), rtol=1e-12)
+    # float form: qr sums land in the float buffer
+    rf = svoc.consensus_float(g.pred.float() * 1e-6, 3)
+    sf = svoc.RunningStats(16)
+    sf.update(rf)
+    np.testing.assert_allclose(sf.qr_sums(False).cpu().numpy(), rf.qr.double().sum(dim=0).cpu().numpy(), rtol=1e-9)
+    assert sf.summary()["rounds"] == 30000
