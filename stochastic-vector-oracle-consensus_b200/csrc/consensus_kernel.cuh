@@ -40,6 +40,9 @@ struct Params {
     int rb;          // rounds per CTA
     int words;       // ceil(N/32)
     int tile_smem;   // 1: rounds staged in shared memory; 0: read from global
+    // wide variant (consensus_wide.cuh): parts per column, rows per part, key column stride (bytes),
+    // threads per row in the row phases, 1 when every round can be fetched by a TMA bulk copy
+    int wP, wRP, wCS, wH, wBulk;
 };
 
 // ------------------------------------------------------------------------------ traits
@@ -440,6 +443,9 @@ __global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) consensus_kernel(const 
 struct Plan {
     int npad, rb, threads, tile_smem;
     size_t smem;
+    int variant;  // 0: small<NPAD> / generic, 1: wide
+    long long grid;
+    int wP, wRP, wCS, wH;
 };
 
 int fail(const std::string &m);

@@ -1,0 +1,585 @@
+// consensus_wide.cuh — the `wide` variant of the fused consensus round: 64 < N <= 512 oracles,
+// 32-bit elements (fp32 / int32).  This is the kernel config 4 (N=256, D=128, fp32) runs.
+//
+// One persistent CTA (512 threads, one per SM) processes one round at a time out of shared
+// memory: the N x D tile arrives by a single TMA bulk copy; a thread owns one (column, row-part)
+// unit, P parts per column.  Order statistics are found without sorting:
+//   1. per column, exact min/max -> every element gets a monotone 7-bit key (0..126, 127 is the
+//      sentinel of padded / dropped rows), packed 4 per word in a transposed, bank-conflict-free
+//      scratch (keysT[column][row], column stride == 16 bytes mod 128);
+//   2. MSB-first bisection over the 7 key bits: counting "key >= pivot" is SWAR — one add puts
+//      the comparison of four keys into the byte MSBs, one AND isolates them, one IDP.4A
+//      accumulates — 3 ALU ops per 4 elements, two LDS.128 per 32 elements;
+//   3. the rows whose key falls in the bucket of the wanted rank (and the next bucket) are
+//      collected (a few per column), insertion-sorted, and the two order statistics read off.
+//      Anything unusual (more than WIDE_CAP candidates, degenerate scale) falls back to the
+//      exact generic bisection for that column only.
+// The second pass reuses the keys: dropped rows are re-keyed to the sentinel.
+// Reference semantics: see consensus_kernel.cuh (contract.cairo:442-503 etc.).
+#pragma once
+#include "consensus_kernel.cuh"
+
+namespace svoc {
+
+constexpr int WIDE_THREADS = 512;
+constexpr int WIDE_CAP = 48;
+
+// monotone map of an element onto [0, 1] for key building
+template <class Tr>
+struct WideKey;
+template <>
+struct WideKey<FloatTr<float>> {
+    struct Scale { float inv, off; };
+    __device__ static __forceinline__ bool make(float lo, float hi, Scale &s) {
+        s.inv = 1.0f / (hi - lo);
+        s.off = -lo * s.inv;
+        return isfinite(s.inv) && isfinite(s.off);
+    }
+    __device__ static __forceinline__ float t(float x, const Scale &s) { return __saturatef(fmaf(x, s.inv, s.off)); }
+};
+template <>
+struct WideKey<FixedTr<int32_t>> {
+    struct Scale { int32_t lo; float inv; };
+    __device__ static __forceinline__ bool make(int32_t lo, int32_t hi, Scale &s) {
+        s.lo = lo;
+        s.inv = 1.0f / (float)((uint32_t)hi - (uint32_t)lo);
+        return true;
+    }
+    __device__ static __forceinline__ float t(int32_t x, const Scale &s) {
+        return __saturatef((float)((uint32_t)x - (uint32_t)s.lo) * s.inv);
+    }
+};
+
+__device__ __forceinline__ unsigned pack4(unsigned a, unsigned b, unsigned c, unsigned d) {
+    return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+}
+
+// number of keys >= cand among `rp` packed byte keys (rp multiple of 32, keys <= 127, 1 <= cand <= 127)
+__device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp, unsigned cand) {
+    const unsigned cb = (128u - cand) * 0x01010101u;
+    unsigned acc = 0;
+    for (int g = 0; g < rp; g += 32) {
+        const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
+        const uint4 b = *reinterpret_cast<const uint4 *>(keys + g + 16);
+        acc = __dp4a((a.x + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((a.y + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((a.z + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((a.w + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((b.x + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((b.y + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((b.z + cb) & 0x80808080u, 0x01010101u, acc);
+        acc = __dp4a((b.w + cb) & 0x80808080u, 0x01010101u, acc);
+    }
+    return acc >> 7;
+}
+
+struct WideCtx {
+    int N, D, P, RP, CS;
+    int c, part;        // this thread's unit
+    bool has_unit;
+    uint8_t *mykeys;    // keysT + c*CS + part*RP
+    int *partial;       // [2][P][D]
+    int *cand_cnt;      // [D]
+    void *list;         // [WIDE_CAP][D] in_t
+    int *flag;          // [D] 0 resolved, 1 needs the minimum above `thr`, 2 needs a finer re-keying
+    void *thr, *rlo, *rhi;          // [D] in_t each
+    uint32_t *wmin, *wmax, *resc;   // [D] order-preserving keys: window min / max, rescue minimum
+};
+
+// 7-bit key of one element.  Level 0: the scale spans the column's exact [min, max] and keys use
+// 0..126.  Refinement levels: the scale spans a sub-range; 0 = below it, 126 = above it, 1..125 inside.
+template <class Tr, bool FIRST>
+__device__ __forceinline__ unsigned wide_key(typename Tr::in_t x, typename Tr::in_t lo, typename Tr::in_t hi,
+                                             const typename WideKey<Tr>::Scale &sc) {
+    const float t = WideKey<Tr>::t(x, sc);
+    if (FIRST) return __float_as_uint(__fmaf_rn(t, 126.0f, 8388608.0f));
+    const unsigned k = __float_as_uint(__fmaf_rn(t, 124.0f, 8388609.0f));   // 1 + round(124 t) in the low byte
+    return x < lo ? 0u : (x > hi ? 126u : k);
+}
+
+template <class Tr, bool FIRST>
+__device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename Tr::in_t *tile, const uint8_t *keep,
+                                                typename Tr::in_t lo, typename Tr::in_t hi,
+                                                const typename WideKey<Tr>::Scale &sc) {
+    const int row_lo = w.part * w.RP;
+    for (int g = 0; g < w.RP; g += 16) {
+        unsigned f[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const int row = row_lo + g + k;
+            f[k] = 127u;
+            if (row < w.N && (!keep || keep[row])) f[k] = wide_key<Tr, FIRST>(tile[(size_t)row * w.D + w.c], lo, hi, sc);
+        }
+        *reinterpret_cast<uint4 *>(w.mykeys + g) =
+            make_uint4(pack4(f[0], f[1], f[2], f[3]), pack4(f[4], f[5], f[6], f[7]), pack4(f[8], f[9], f[10], f[11]),
+                       pack4(f[12], f[13], f[14], f[15]));
+    }
+}
+
+// Centre of the flagged rows of every column (all rows when keep == nullptr).  Must be called by
+// all threads of the CTA (it synchronises); the result is valid in the part-0 thread of a column.
+template <class Tr>
+__device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, const typename Tr::in_t *tile,
+                                                          const uint8_t *keep, int n_valid, int kind, bool col_const,
+                                                          bool col_fallback, typename Tr::in_t const_value, int &buf,
+                                                          bool &refined) {
+    using in_t = typename Tr::in_t;
+    using val_t = typename Tr::val_t;
+    using Key = WideKey<Tr>;
+    refined = false;
+    val_t centre = 0;
+    if (kind == SVOC_CENTRE_MEAN) {
+        if (w.has_unit && w.part == 0) {
+            val_t s = 0;
+            for (int i = 0; i < w.N; ++i)
+                if (!keep || keep[i]) s += (val_t)tile[(size_t)i * w.D + w.c];
+            centre = Tr::mean(s, n_valid);
+        }
+        return centre;
+    }
+    int klo, khi;
+    centre_ranks(kind, n_valid, klo, khi);
+    in_t *list = reinterpret_cast<in_t *>(w.list);
+    in_t *thr = reinterpret_cast<in_t *>(w.thr), *rlo = reinterpret_cast<in_t *>(w.rlo), *rhi = reinterpret_cast<in_t *>(w.rhi);
+    const int slots = w.P * w.RP;
+    const int row_lo = w.part * w.RP, row_hi = min(w.N, row_lo + w.RP);
+    bool done = !w.has_unit || col_const;
+    in_t v_lo = const_value, v_hi = const_value;
+    bool have_centre = false;
+
+    for (;;) {
+        const bool active = !done;
+        // ---- bisection over the 7 key bits for rank klo
+        unsigned prefix = 0;
+        int L = 0;
+        for (int bit = 6; bit >= 0; --bit) {
+            const unsigned cand = prefix | (1u << bit);
+            if (active) w.partial[(buf * w.P + w.part) * w.D + w.c] = (int)count_ge(w.mykeys, w.RP, cand);
+            __syncthreads();
+            if (active) {
+                int tot = 0;
+                for (int q = 0; q < w.P; ++q) tot += w.partial[(buf * w.P + q) * w.D + w.c];
+                const int lt = slots - tot;  // sentinels (127) are never below a pivot
+                if (lt <= klo) { prefix = cand; L = lt; }
+            }
+            buf ^= 1;
+        }
+        // ---- collect the rows whose key lies in the window [prefix, prefix + 4)
+        if (active) {
+            const unsigned up = prefix + 4 > 127u ? 127u : prefix + 4;
+            const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
+            uint32_t kmin = 0xffffffffu, kmax = 0u;
+            for (int g = 0; g < w.RP; g += 32) {
+                const uint4 a = *reinterpret_cast<const uint4 *>(w.mykeys + g);
+                const uint4 b = *reinterpret_cast<const uint4 *>(w.mykeys + g + 16);
+                unsigned acc = (a.x + c1b) & ~(a.x + c2b) & 0x80808080u;
+                acc |= ((a.y + c1b) & ~(a.y + c2b) & 0x80808080u) >> 1;
+                acc |= ((a.z + c1b) & ~(a.z + c2b) & 0x80808080u) >> 2;
+                acc |= ((a.w + c1b) & ~(a.w + c2b) & 0x80808080u) >> 3;
+                acc |= ((b.x + c1b) & ~(b.x + c2b) & 0x80808080u) >> 4;
+                acc |= ((b.y + c1b) & ~(b.y + c2b) & 0x80808080u) >> 5;
+                acc |= ((b.z + c1b) & ~(b.z + c2b) & 0x80808080u) >> 6;
+                acc |= ((b.w + c1b) & ~(b.w + c2b) & 0x80808080u) >> 7;
+                while (acc) {
+                    const int pos = __ffs(acc) - 1;
+                    acc &= acc - 1;
+                    const int row = row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3);
+                    const in_t x = tile[(size_t)row * w.D + w.c];
+                    const uint32_t kx = okey(x);
+                    kmin = kx < kmin ? kx : kmin;
+                    kmax = kx > kmax ? kx : kmax;
+                    const int slot = atomicAdd(&w.cand_cnt[w.c], 1);
+                    if (slot < WIDE_CAP) list[slot * w.D + w.c] = x;
+                }
+            }
+            if (kmin <= kmax) {
+                atomicMin(&w.wmin[w.c], kmin);
+                atomicMax(&w.wmax[w.c], kmax);
+            }
+        }
+        __syncthreads();
+        // ---- decision per column (part-0 thread)
+        int flag = 0;
+        if (active && w.part == 0) {
+            const int m = w.cand_cnt[w.c];   // rows in the window (not capped)
+            const int j1 = klo - L, j2 = khi - L;
+            if (col_fallback) {
+                val_t sk, ku;
+                int stw = STW_OK;
+                centre = column_centre_generic<Tr>(tile + w.c, w.D, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                have_centre = true;
+            } else if (m <= WIDE_CAP) {
+                for (int a = 1; a < m; ++a) {
+                    const in_t v = list[a * w.D + w.c];
+                    int b = a - 1;
+                    while (b >= 0 && list[b * w.D + w.c] > v) {
+                        list[(b + 1) * w.D + w.c] = list[b * w.D + w.c];
+                        --b;
+                    }
+                    list[(b + 1) * w.D + w.c] = v;
+                }
+                v_lo = list[j1 * w.D + w.c];
+                if (j2 < m) v_hi = list[j2 * w.D + w.c];
+                else { flag = 1; thr[w.c] = list[(m - 1) * w.D + w.c]; }
+            } else {
+                in_t a, b;
+                unkey(w.wmin[w.c], a);
+                unkey(w.wmax[w.c], b);
+                typename Key::Scale sc;
+                if (!(b > a)) {              // the whole window is one value
+                    v_lo = a;
+                    if (j2 < m) v_hi = a;
+                    else { flag = 1; thr[w.c] = a; }
+                } else if (!Key::make(a, b, sc)) {
+                    val_t sk, ku;
+                    int stw = STW_OK;
+                    centre = column_centre_generic<Tr>(tile + w.c, w.D, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                    have_centre = true;
+                } else {
+                    flag = 2;
+                    rlo[w.c] = a;
+                    rhi[w.c] = b;
+                }
+            }
+            w.flag[w.c] = flag;
+            w.cand_cnt[w.c] = 0;
+            w.wmin[w.c] = 0xffffffffu;
+            w.wmax[w.c] = 0u;
+            w.resc[w.c] = 0xffffffffu;
+        }
+        if (!__syncthreads_or(flag)) break;   // common case: every column resolved
+        const int f = active ? w.flag[w.c] : 0;
+        if (f == 1) {                          // minimum of the flagged rows above the window
+            const in_t t0 = thr[w.c];
+            uint32_t best = 0xffffffffu;
+            for (int row = row_lo; row < row_hi; ++row) {
+                if (keep && !keep[row]) continue;
+                const in_t x = tile[(size_t)row * w.D + w.c];
+                if (x > t0) { const uint32_t kx = okey(x); best = kx < best ? kx : best; }
+            }
+            if (best != 0xffffffffu) atomicMin(&w.resc[w.c], best);
+        } else if (f == 2) {                   // finer keys over the window's value range
+            const in_t a = rlo[w.c], b = rhi[w.c];
+            typename Key::Scale sc;
+            Key::make(a, b, sc);
+            wide_build_keys<Tr, false>(w, tile, keep, a, b, sc);
+            refined = true;
+        }
+        const int more = __syncthreads_or(f == 2);
+        if (f == 1 && w.part == 0) unkey(w.resc[w.c], v_hi);
+        if (f != 2) done = true;
+        if (!more) break;
+    }
+    if (w.has_unit && w.part == 0 && !have_centre) centre = Tr::half_sum((val_t)v_lo, (val_t)v_hi);
+    return centre;
+}
+
+template <class Tr>
+__global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const Params p) {
+    using in_t = typename Tr::in_t;
+    using val_t = typename Tr::val_t;
+    using acc_t = typename Tr::acc_t;
+    using Key = WideKey<Tr>;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int N = p.N, D = p.D, R = p.R, P = p.wP, RP = p.wRP, CS = p.wCS, H = p.wH;
+    const int tid = threadIdx.x;
+    auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+
+    size_t off = 0;
+    in_t *tile = reinterpret_cast<in_t *>(smem_raw);            off += al((size_t)N * D * sizeof(in_t));
+    val_t *c1 = reinterpret_cast<val_t *>(smem_raw + off);      off += al((size_t)D * sizeof(val_t));
+    acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + off);    off += al((size_t)N * sizeof(acc_t));
+    acc_t *qrp = reinterpret_cast<acc_t *>(smem_raw + off);     off += al((size_t)H * N * sizeof(acc_t));
+    u64 *bar = reinterpret_cast<u64 *>(smem_raw + off);         off += 16;
+    uint8_t *keysT = smem_raw + off;                            off += al((size_t)D * CS);
+    in_t *list = reinterpret_cast<in_t *>(smem_raw + off);      off += al((size_t)WIDE_CAP * D * sizeof(in_t));
+    in_t *smin = reinterpret_cast<in_t *>(smem_raw + off);      off += al((size_t)P * D * sizeof(in_t));
+    in_t *smax = reinterpret_cast<in_t *>(smem_raw + off);      off += al((size_t)P * D * sizeof(in_t));
+    int *partial = reinterpret_cast<int *>(smem_raw + off);     off += al((size_t)2 * P * D * sizeof(int));
+    int *cand_cnt = reinterpret_cast<int *>(smem_raw + off);    off += al((size_t)D * sizeof(int));
+    int *rankp = reinterpret_cast<int *>(smem_raw + off);       off += al((size_t)H * N * sizeof(int));
+    uint32_t *maskw = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)(P * RP / 32 + 1) * 4);
+    int *stw_s = reinterpret_cast<int *>(smem_raw + off);       off += 16;
+    int *flag_s = reinterpret_cast<int *>(smem_raw + off);      off += al((size_t)D * 4);
+    in_t *thr_s = reinterpret_cast<in_t *>(smem_raw + off);     off += al((size_t)D * sizeof(in_t));
+    in_t *rlo_s = reinterpret_cast<in_t *>(smem_raw + off);     off += al((size_t)D * sizeof(in_t));
+    in_t *rhi_s = reinterpret_cast<in_t *>(smem_raw + off);     off += al((size_t)D * sizeof(in_t));
+    uint32_t *wmin_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
+    uint32_t *wmax_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
+    uint32_t *resc_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
+    uint8_t *keep_s = smem_raw + off;
+
+    WideCtx w;
+    w.N = N; w.D = D; w.P = P; w.RP = RP; w.CS = CS;
+    w.has_unit = tid < D * P;
+    w.c = w.has_unit ? tid % D : 0;
+    w.part = w.has_unit ? tid / D : 0;
+    w.mykeys = keysT + (size_t)w.c * CS + (size_t)w.part * RP;
+    w.partial = partial;
+    w.cand_cnt = cand_cnt;
+    w.list = list;
+    w.flag = flag_s; w.thr = thr_s; w.rlo = rlo_s; w.rhi = rhi_s;
+    w.wmin = wmin_s; w.wmax = wmax_s; w.resc = resc_s;
+
+    const size_t round_elems = (size_t)N * D;
+    const uint32_t round_bytes = (uint32_t)(round_elems * sizeof(in_t));
+    if (tid == 0) mbar_init(bar, 1);
+    for (int k = tid; k < D; k += WIDE_THREADS) {
+        cand_cnt[k] = 0;
+        wmin_s[k] = 0xffffffffu;
+        wmax_s[k] = 0u;
+        resc_s[k] = 0xffffffffu;
+        flag_s[k] = 0;
+    }
+    __syncthreads();
+    uint32_t parity = 0;
+    int buf = 0;
+    const int row_lo = w.part * RP, row_hi = min(N, (w.part + 1) * RP);
+    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+
+    for (i64 r = blockIdx.x; r < p.T; r += gridDim.x) {
+        const in_t *gsrc = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;
+        // ---- phase 0: stage the round
+        if (p.wBulk) {
+            if (tid == 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads of the old tile before the async write
+                mbar_expect_tx(bar, round_bytes);
+                bulk_g2s(tile, gsrc, round_bytes, bar);
+            }
+            mbar_wait(bar, parity);
+            parity ^= 1;
+        } else {
+            for (size_t e = tid; e < round_elems; e += WIDE_THREADS) tile[e] = gsrc[e];
+        }
+        if (tid == 0) *stw_s = STW_OK;
+        __syncthreads();
+
+        // ---- phase 1a: exact column min / max
+        if (w.has_unit) {
+            in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
+            for (int row = row_lo; row < row_hi; ++row) {
+                const in_t x = tile[(size_t)row * D + w.c];
+                lo = x < lo ? x : lo;
+                hi = x > hi ? x : hi;
+            }
+            smin[w.part * D + w.c] = lo;
+            smax[w.part * D + w.c] = hi;
+        }
+        __syncthreads();
+        // ---- phase 1b: 7-bit keys of this unit's rows
+        bool col_const = false, col_fb = false;
+        in_t cval = 0, lo0 = 0, hi0 = 0;
+        typename Key::Scale sc0{};
+        if (w.has_unit) {
+            in_t lo = smin[w.c], hi = smax[w.c];
+            for (int q = 1; q < P; ++q) {
+                const in_t a = smin[q * D + w.c], b = smax[q * D + w.c];
+                lo = a < lo ? a : lo;
+                hi = b > hi ? b : hi;
+            }
+            col_const = !(hi > lo);
+            cval = lo;
+            typename Key::Scale sc;
+            col_fb = !col_const && !Key::make(lo, hi, sc);
+            if (!col_const && !col_fb) {
+                wide_build_keys<Tr, true>(w, tile, nullptr, lo, hi, sc);
+            } else {
+                for (int g = 0; g < RP; g += 16) *reinterpret_cast<uint4 *>(w.mykeys + g) = make_uint4(0, 0, 0, 0);
+            }
+            lo0 = lo; hi0 = hi; sc0 = sc;
+        }
+        // ---- phase 1c: first-pass centre
+        bool refined1 = false, refined2 = false;
+        const val_t e1 = wide_centre<Tr>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
+        if (w.has_unit && w.part == 0) {
+            c1[w.c] = e1;
+            if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * D + w.c] = e1;
+        }
+        __syncthreads();
+
+        // ---- phase 2: quadratic risk of every row (H threads per row, each a slice of the dimensions)
+        if (tid < N * H) {
+            const int i = tid % N, h = tid / N;
+            const int dh = (D + H - 1) / H, dlo = h * dh, dhi = min(D, dlo + dh);
+            acc_t q = 0;
+            bool bad = false;
+            if (dlo < dhi) {
+                const in_t *row = tile + (size_t)i * D;
+                int d = dlo + i % (dhi - dlo);  // rotated start keeps the reads conflict-free
+                for (int k = dlo; k < dhi; ++k) {
+                    const in_t x = row[d];
+                    if constexpr (Tr::fixed) {
+                        if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
+                        else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+                    }
+                    q += Tr::dev(x, c1[d]);
+                    d = (d + 1 == dhi) ? dlo : d + 1;
+                }
+            }
+            qrp[h * N + i] = q;
+            if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
+        }
+        __syncthreads();
+        if (tid < N) {
+            acc_t q = 0;
+            for (int h = 0; h < H; ++h) q += qrp[h * N + tid];
+            qr_s[tid] = q;
+            if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * N + tid] = q;
+        }
+        __syncthreads();
+
+        // ---- phase 3a: rank of every row under (qr asc, index desc | asc)
+        if (tid < N * H) {
+            const int i = tid % N, h = tid / N;
+            const int jh = (N + H - 1) / H, jlo = h * jh, jhi = min(N, jlo + jh);
+            const acc_t mine = qr_s[i];
+            int rank = 0;
+            if (p.tie == SVOC_TIE_HIGH_INDEX_KEPT) {
+                for (int j = jlo; j < jhi; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j > i)) ? 1 : 0;
+            } else {
+                for (int j = jlo; j < jhi; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j < i)) ? 1 : 0;
+            }
+            rankp[h * N + i] = rank;
+        }
+        __syncthreads();
+        {
+            // keep flags + packed mask words (one ballot per warp of rows)
+            const int slots = P * RP;
+            bool keepme = false;
+            if (tid < N) {
+                int rank = 0;
+                for (int h = 0; h < H; ++h) rank += rankp[h * N + tid];
+                keepme = rank < R;
+                keep_s[tid] = keepme ? 1 : 0;
+            }
+            if (tid < slots || tid < ((N + 31) & ~31)) {
+                const unsigned bits = __ballot_sync(0xffffffffu, keepme);
+                if ((tid & 31) == 0) {
+                    maskw[tid >> 5] = bits;
+                    if (p.reliable && (tid >> 5) < p.words) p.reliable[(size_t)r * p.words + (tid >> 5)] = bits;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- phase 3b: reliabilities (warp 0) while the other warps re-key the dropped rows
+        if (tid < 32) {
+            acc_t s1 = 0, s2 = 0;
+            for (int i = tid; i < N; i += 32) {
+                const acc_t q = qr_s[i];
+                s1 += q;
+                if (keep_s[i]) s2 += q;
+            }
+            for (int o = 16; o; o >>= 1) {
+                s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            }
+            if (tid == 0) {
+                int stw = STW_OK;
+                if constexpr (Tr::fixed) {
+                    const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
+                    if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
+                    i64 rel2 = 0;
+                    if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                    else {
+                        rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
+                        if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+                    }
+                    reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
+                    reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
+                } else {
+                    const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
+                    if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
+                    val_t rel2 = 0;
+                    if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                    else {
+                        rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
+                        if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
+                    }
+                    reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
+                    reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
+                }
+                if (stw != STW_OK) atomicMin(stw_s, stw);
+            }
+        }
+        // level-0 keys of the kept rows, sentinel for the dropped ones (the first pass may have left
+        // refined keys behind, so the unit is re-keyed rather than patched)
+        if (w.has_unit && !col_const && !col_fb) {
+            if (refined1) {
+                wide_build_keys<Tr, true>(w, tile, keep_s, lo0, hi0, sc0);
+            } else {
+                for (int g = 0; g < RP; g += 32) {   // dropped rows of this unit -> sentinel key
+                    const int base = row_lo + g;
+                    unsigned drop = ~maskw[base >> 5];
+                    if (base + 32 > N) drop &= (base < N) ? ((1u << (N - base)) - 1u) : 0u;
+                    while (drop) {
+                        const int b = __ffs(drop) - 1;
+                        drop &= drop - 1;
+                        w.mykeys[g + b] = 127;
+                    }
+                }
+            }
+        }
+        // ---- phase 4: second-pass centre over the reliable rows (+ moments)
+        val_t cons = 0;
+        if (!shape2) cons = wide_centre<Tr>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
+        if (w.has_unit && w.part == 0) {
+            reinterpret_cast<val_t *>(p.consensus)[(size_t)r * D + w.c] = cons;
+            if (p.want_moments) {
+                val_t sk = 0, ku = 0;
+                int stw = STW_OK;
+                if (!shape2) {
+                    const in_t *col = tile + w.c;
+                    auto fe = [&](auto f) {
+                        for (int i = 0; i < N; ++i)
+                            if (keep_s[i]) f(col[(size_t)i * D]);
+                    };
+                    column_moments<Tr>(fe, R, sk, ku, stw);
+                }
+                if (p.skew) reinterpret_cast<val_t *>(p.skew)[(size_t)r * D + w.c] = sk;
+                if (p.kurt) reinterpret_cast<val_t *>(p.kurt)[(size_t)r * D + w.c] = ku;
+                if (stw != STW_OK) atomicMin(stw_s, stw);
+            }
+        }
+        __syncthreads();  // every read of the tile is done: the next round may overwrite it
+        if (tid == 0) {
+            const int sw = *stw_s;
+            p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+        }
+    }
+}
+
+// shared-memory footprint of the wide variant (must match the carve-up above)
+inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t es, size_t vs) {
+    auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+    size_t s = 0;
+    s += al((size_t)N * D * es);
+    s += al((size_t)D * vs);
+    s += al((size_t)N * vs);
+    s += al((size_t)H * N * vs);
+    s += 16;
+    s += al((size_t)D * CS);
+    s += al((size_t)WIDE_CAP * D * es);
+    s += 2 * al((size_t)P * D * es);
+    s += al((size_t)2 * P * D * 4);
+    s += al((size_t)D * 4);
+    s += al((size_t)H * N * 4);
+    s += al((size_t)(P * RP / 32 + 1) * 4);
+    s += 16;
+    s += al((size_t)D * 4) + 3 * al((size_t)D * es) + 3 * al((size_t)D * 4);
+    s += al((size_t)N);
+    return s;
+}
+
+template <class Tr>
+int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
+    auto kern = consensus_wide_kernel<Tr>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+    if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    kern<<<(unsigned)pl.grid, WIDE_THREADS, pl.smem, st>>>(p);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
+    count_launch();
+    return 0;
+}
+
+}  // namespace svoc

@@ -5,7 +5,9 @@
 #include <mutex>
 #include <string>
 
-#include "consensus_kernel.cuh"
+#include <algorithm>
+
+#include "consensus_wide.cuh"
 
 namespace svoc {
 
@@ -37,8 +39,49 @@ static size_t smem_bytes(const svoc_config &c, int rb, int tile_smem) {
     return s;
 }
 
-static Plan make_plan(const svoc_config &c) {
-    Plan pl;
+static int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+    }
+    return n;
+}
+
+// wide variant: 64 < N <= 512, 32-bit elements, one (column, row-part) unit per thread
+static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
+    const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
+    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
+    if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
+    int P = 1;
+    while (P * 2 <= 8 && P * 2 * D <= 512 && P * 2 * 32 <= N) P *= 2;
+    const int RP = (((N + P - 1) / P) + 31) & ~31;
+    if (P * RP > 512) return false;
+    int CS = P * RP;
+    while ((CS / 4) % 32 != 4) CS += 16;
+    int H = 1;
+    while (H * 2 * N <= 512 && H * 2 <= D) H *= 2;
+    const size_t smem = wide_smem_bytes(N, D, P, RP, CS, H, 4, c.dtype == SVOC_F32 ? 4 : 8);
+    if (smem > 227 * 1024) return false;
+    pl.variant = 1;
+    pl.wP = P; pl.wRP = RP; pl.wCS = CS; pl.wH = H;
+    pl.smem = smem;
+    pl.threads = 512;
+    pl.rb = 1;
+    pl.npad = 0;
+    pl.tile_smem = 1;
+    (void)pred;
+    return true;
+}
+
+static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
+    Plan pl{};
+    if (plan_wide(c, pred, pl)) {
+        pl.grid = std::min<long long>(T, sm_count());
+        return pl;
+    }
+    pl.variant = 0;
     pl.npad = npad_for(c.n_oracles);
     pl.threads = pl.npad ? 128 : 256;
     const size_t budget = pl.npad ? 40 * 1024 : 200 * 1024;
@@ -48,6 +91,7 @@ static Plan make_plan(const svoc_config &c) {
     pl.tile_smem = smem_bytes(c, rb, 1) <= 200 * 1024 ? 1 : 0;
     pl.rb = rb;
     pl.smem = smem_bytes(c, rb, pl.tile_smem);
+    pl.grid = (T + rb - 1) / rb;
     return pl;
 }
 
@@ -97,6 +141,9 @@ static Params make_params(const svoc_config &c, const void *pred, int64_t T, con
     p.rb = pl.rb;
     p.words = (c.n_oracles + 31) / 32;
     p.tile_smem = pl.tile_smem;
+    p.wP = pl.wP; p.wRP = pl.wRP; p.wCS = pl.wCS; p.wH = pl.wH;
+    const size_t round_bytes = (size_t)c.n_oracles * c.dimension * elem_size(c.dtype);
+    p.wBulk = ((reinterpret_cast<uintptr_t>(pred) & 15) == 0 && (round_bytes & 15) == 0 && round_bytes < (1u << 20)) ? 1 : 0;
     return p;
 }
 
@@ -104,7 +151,7 @@ int consensus_device(const svoc_config *cfg, const void *pred, int64_t T, const 
                      bool fixed) {
     if (int rc = validate(cfg, pred, T, out, fixed)) return rc;
     if (T == 0) return 0;
-    const Plan pl = make_plan(*cfg);
+    const Plan pl = make_plan(*cfg, pred, T);
     const Params p = make_params(*cfg, pred, T, *out, pl);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (cfg->dtype) {
@@ -146,7 +193,9 @@ const char *svoc_kernel_variant(const svoc_config *cfg) {
     static thread_local char buf[32];
     if (!cfg) return "invalid";
     const int np = svoc::npad_for(cfg->n_oracles);
-    if (np) snprintf(buf, sizeof buf, "small%d", np);
+    svoc::Plan pl{};
+    if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
+    else if (np) snprintf(buf, sizeof buf, "small%d", np);
     else snprintf(buf, sizeof buf, "generic");
     return buf;
 }
