@@ -50,6 +50,11 @@ struct WideKey<FixedTr<int32_t>> {
     }
 };
 
+__device__ __forceinline__ float vmin(float a, float b) { return fminf(a, b); }
+__device__ __forceinline__ float vmax(float a, float b) { return fmaxf(a, b); }
+__device__ __forceinline__ int32_t vmin(int32_t a, int32_t b) { return min(a, b); }
+__device__ __forceinline__ int32_t vmax(int32_t a, int32_t b) { return max(a, b); }
+
 __device__ __forceinline__ unsigned pack4(unsigned a, unsigned b, unsigned c, unsigned d) {
     return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
 }
@@ -83,6 +88,7 @@ struct WideCtx {
     void *list;         // [WIDE_CAP][D] in_t
     int *flag;          // [D] 0 resolved, 1 needs the minimum above `thr`, 2 needs a finer re-keying
     void *thr, *rlo, *rhi;          // [D] in_t each
+    void *res_lo, *res_hi;          // [D] in_t: the two order statistics found by the rank phase
     uint32_t *wmin, *wmax, *resc;   // [D] order-preserving keys: window min / max, rescue minimum
 };
 
@@ -102,14 +108,16 @@ __device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename
                                                 typename Tr::in_t lo, typename Tr::in_t hi,
                                                 const typename WideKey<Tr>::Scale &sc) {
     const int row_lo = w.part * w.RP;
+    const typename Tr::in_t *ptr = tile + row_lo * w.D + w.c;
     for (int g = 0; g < w.RP; g += 16) {
         unsigned f[16];
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
             const int row = row_lo + g + k;
             f[k] = 127u;
-            if (row < w.N && (!keep || keep[row])) f[k] = wide_key<Tr, FIRST>(tile[(size_t)row * w.D + w.c], lo, hi, sc);
+            if (row < w.N && (!keep || keep[row])) f[k] = wide_key<Tr, FIRST>(ptr[k * w.D], lo, hi, sc);
         }
+        ptr += 16 * w.D;
         *reinterpret_cast<uint4 *>(w.mykeys + g) =
             make_uint4(pack4(f[0], f[1], f[2], f[3]), pack4(f[4], f[5], f[6], f[7]), pack4(f[8], f[9], f[10], f[11]),
                        pack4(f[12], f[13], f[14], f[15]));
@@ -164,9 +172,9 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
             }
             buf ^= 1;
         }
-        // ---- collect the rows whose key lies in the window [prefix, prefix + 4)
+        // ---- collect the rows whose key lies in the window [prefix, prefix + 3)
         if (active) {
-            const unsigned up = prefix + 4 > 127u ? 127u : prefix + 4;
+            const unsigned up = prefix + 3 > 127u ? 127u : prefix + 3;
             const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
             uint32_t kmin = 0xffffffffu, kmax = 0u;
             for (int g = 0; g < w.RP; g += 32) {
@@ -184,7 +192,7 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                     const int pos = __ffs(acc) - 1;
                     acc &= acc - 1;
                     const int row = row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3);
-                    const in_t x = tile[(size_t)row * w.D + w.c];
+                    const in_t x = tile[row * w.D + w.c];
                     const uint32_t kx = okey(x);
                     kmin = kx < kmin ? kx : kmin;
                     kmax = kx > kmax ? kx : kmax;
@@ -198,38 +206,44 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
             }
         }
         __syncthreads();
-        // ---- decision per column (part-0 thread)
+        // ---- the two order statistics: the P threads of a column rank the window's rows between them
         int flag = 0;
-        if (active && w.part == 0) {
+        in_t *res_lo = reinterpret_cast<in_t *>(w.res_lo), *res_hi = reinterpret_cast<in_t *>(w.res_hi);
+        if (active) {
             const int m = w.cand_cnt[w.c];   // rows in the window (not capped)
             const int j1 = klo - L, j2 = khi - L;
             if (col_fallback) {
-                val_t sk, ku;
-                int stw = STW_OK;
-                centre = column_centre_generic<Tr>(tile + w.c, w.D, w.N, keep, n_valid, kind, false, sk, ku, stw);
-                have_centre = true;
-            } else if (m <= WIDE_CAP) {
-                for (int a = 1; a < m; ++a) {
-                    const in_t v = list[a * w.D + w.c];
-                    int b = a - 1;
-                    while (b >= 0 && list[b * w.D + w.c] > v) {
-                        list[(b + 1) * w.D + w.c] = list[b * w.D + w.c];
-                        --b;
-                    }
-                    list[(b + 1) * w.D + w.c] = v;
+                if (w.part == 0) {
+                    val_t sk, ku;
+                    int stw = STW_OK;
+                    centre = column_centre_generic<Tr>(tile + w.c, w.D, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                    have_centre = true;
                 }
-                v_lo = list[j1 * w.D + w.c];
-                if (j2 < m) v_hi = list[j2 * w.D + w.c];
-                else { flag = 1; thr[w.c] = list[(m - 1) * w.D + w.c]; }
-            } else {
+            } else if (m <= WIDE_CAP) {
+                const in_t *lc = list + w.c;
+                for (int a = w.part; a < m; a += w.P) {
+                    const in_t v = lc[a * w.D];
+                    int below = 0, equal_before = 0;
+                    for (int b = 0; b < m; ++b) {
+                        const in_t u = lc[b * w.D];
+                        below += u < v ? 1 : 0;
+                        equal_before += (u == v && b < a) ? 1 : 0;
+                    }
+                    const int rk = below + equal_before;
+                    if (rk == j1) res_lo[w.c] = v;
+                    if (rk == j2) res_hi[w.c] = v;
+                    if (rk == m - 1 && j2 >= m) thr[w.c] = v;   // window maximum, for the rescue scan
+                }
+                if (j2 >= m) flag = 1;
+            } else if (w.part == 0) {
                 in_t a, b;
                 unkey(w.wmin[w.c], a);
                 unkey(w.wmax[w.c], b);
                 typename Key::Scale sc;
                 if (!(b > a)) {              // the whole window is one value
-                    v_lo = a;
-                    if (j2 < m) v_hi = a;
-                    else { flag = 1; thr[w.c] = a; }
+                    res_lo[w.c] = a;
+                    res_hi[w.c] = a;
+                    if (j2 >= m) { flag = 1; thr[w.c] = a; }
                 } else if (!Key::make(a, b, sc)) {
                     val_t sk, ku;
                     int stw = STW_OK;
@@ -241,20 +255,27 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                     rhi[w.c] = b;
                 }
             }
-            w.flag[w.c] = flag;
-            w.cand_cnt[w.c] = 0;
-            w.wmin[w.c] = 0xffffffffu;
-            w.wmax[w.c] = 0u;
-            w.resc[w.c] = 0xffffffffu;
+            if (w.part == 0) {
+                w.flag[w.c] = flag;
+                w.wmin[w.c] = 0xffffffffu;
+                w.wmax[w.c] = 0u;
+                w.resc[w.c] = 0xffffffffu;
+            }
         }
-        if (!__syncthreads_or(flag)) break;   // common case: every column resolved
+        const int any = __syncthreads_or(flag);
+        if (active && w.part == 0) {
+            w.cand_cnt[w.c] = 0;   // everyone has read it; the next collect comes after more barriers
+            if (!have_centre) { v_lo = res_lo[w.c]; v_hi = res_hi[w.c]; }
+        }
+        if (!any) break;            // common case: every column resolved
         const int f = active ? w.flag[w.c] : 0;
         if (f == 1) {                          // minimum of the flagged rows above the window
             const in_t t0 = thr[w.c];
             uint32_t best = 0xffffffffu;
-            for (int row = row_lo; row < row_hi; ++row) {
+            const in_t *ptr = tile + row_lo * w.D + w.c;
+            for (int row = row_lo; row < row_hi; ++row, ptr += w.D) {
                 if (keep && !keep[row]) continue;
-                const in_t x = tile[(size_t)row * w.D + w.c];
+                const in_t x = *ptr;
                 if (x > t0) { const uint32_t kx = okey(x); best = kx < best ? kx : best; }
             }
             if (best != 0xffffffffu) atomicMin(&w.resc[w.c], best);
@@ -267,6 +288,7 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
         }
         const int more = __syncthreads_or(f == 2);
         if (f == 1 && w.part == 0) unkey(w.resc[w.c], v_hi);
+        if (f == 2 && w.part == 0) { v_lo = const_value; v_hi = const_value; }
         if (f != 2) done = true;
         if (!more) break;
     }
@@ -307,6 +329,8 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
     uint32_t *wmin_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
     uint32_t *wmax_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
     uint32_t *resc_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
+    in_t *reslo_s = reinterpret_cast<in_t *>(smem_raw + off);   off += al((size_t)D * sizeof(in_t));
+    in_t *reshi_s = reinterpret_cast<in_t *>(smem_raw + off);   off += al((size_t)D * sizeof(in_t));
     uint8_t *keep_s = smem_raw + off;
 
     WideCtx w;
@@ -320,6 +344,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
     w.list = list;
     w.flag = flag_s; w.thr = thr_s; w.rlo = rlo_s; w.rhi = rhi_s;
     w.wmin = wmin_s; w.wmax = wmax_s; w.resc = resc_s;
+    w.res_lo = reslo_s; w.res_hi = reshi_s;
 
     const size_t round_elems = (size_t)N * D;
     const uint32_t round_bytes = (uint32_t)(round_elems * sizeof(in_t));
@@ -357,10 +382,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         // ---- phase 1a: exact column min / max
         if (w.has_unit) {
             in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
-            for (int row = row_lo; row < row_hi; ++row) {
-                const in_t x = tile[(size_t)row * D + w.c];
-                lo = x < lo ? x : lo;
-                hi = x > hi ? x : hi;
+            const in_t *ptr = tile + row_lo * D + w.c;
+#pragma unroll 8
+            for (int row = row_lo; row < row_hi; ++row, ptr += D) {
+                const in_t x = *ptr;
+                lo = vmin(lo, x);
+                hi = vmax(hi, x);
             }
             smin[w.part * D + w.c] = lo;
             smax[w.part * D + w.c] = hi;
@@ -374,8 +401,8 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
             in_t lo = smin[w.c], hi = smax[w.c];
             for (int q = 1; q < P; ++q) {
                 const in_t a = smin[q * D + w.c], b = smax[q * D + w.c];
-                lo = a < lo ? a : lo;
-                hi = b > hi ? b : hi;
+                lo = vmin(lo, a);
+                hi = vmax(hi, b);
             }
             col_const = !(hi > lo);
             cval = lo;
@@ -397,23 +424,40 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         }
         __syncthreads();
 
-        // ---- phase 2: quadratic risk of every row (H threads per row, each a slice of the dimensions)
+        // ---- phase 2: quadratic risk of every row (H threads per row, each a slice of the dimensions).
+        //      128-bit shared loads, start rotated by 16 bytes per row so that the 8 lanes of a
+        //      quarter-warp hit 8 different bank groups.
         if (tid < N * H) {
             const int i = tid % N, h = tid / N;
-            const int dh = (D + H - 1) / H, dlo = h * dh, dhi = min(D, dlo + dh);
+            const int dh = (((D + H - 1) / H) + 3) & ~3, dlo = h * dh, dhi = min(D, dlo + dh);
             acc_t q = 0;
             bool bad = false;
+            auto one = [&](in_t x, val_t c) {
+                if constexpr (Tr::fixed) {
+                    if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
+                    else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+                }
+                q += Tr::dev(x, c);
+            };
             if (dlo < dhi) {
-                const in_t *row = tile + (size_t)i * D;
-                int d = dlo + i % (dhi - dlo);  // rotated start keeps the reads conflict-free
-                for (int k = dlo; k < dhi; ++k) {
-                    const in_t x = row[d];
-                    if constexpr (Tr::fixed) {
-                        if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
-                        else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+                const in_t *row = tile + i * D;
+                if ((D & 3) == 0) {
+                    const int ng = (dhi - dlo) >> 2;          // groups of 4 dimensions
+                    int g = i % ng;
+                    for (int k = 0; k < ng; ++k) {
+                        const int d = dlo + 4 * g;
+                        const int4 xv = *reinterpret_cast<const int4 *>(row + d);
+                        in_t x0, x1, x2, x3;
+                        memcpy(&x0, &xv.x, 4); memcpy(&x1, &xv.y, 4); memcpy(&x2, &xv.z, 4); memcpy(&x3, &xv.w, 4);
+                        one(x0, c1[d]); one(x1, c1[d + 1]); one(x2, c1[d + 2]); one(x3, c1[d + 3]);
+                        g = (g + 1 == ng) ? 0 : g + 1;
                     }
-                    q += Tr::dev(x, c1[d]);
-                    d = (d + 1 == dhi) ? dlo : d + 1;
+                } else {
+                    int d = dlo + i % (dhi - dlo);
+                    for (int k = dlo; k < dhi; ++k) {
+                        one(row[d], c1[d]);
+                        d = (d + 1 == dhi) ? dlo : d + 1;
+                    }
                 }
             }
             qrp[h * N + i] = q;
@@ -428,18 +472,29 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         }
         __syncthreads();
 
-        // ---- phase 3a: rank of every row under (qr asc, index desc | asc)
-        if (tid < N * H) {
-            const int i = tid % N, h = tid / N;
-            const int jh = (N + H - 1) / H, jlo = h * jh, jhi = min(N, jlo + jh);
+        // ---- phase 3a: rank of every row under (qr asc, index desc | asc).  For the rows of one warp the
+        //      oracles below the warp's first row and above its last row need a single compare each
+        //      (strict or non-strict by side); only the warp's own index range needs the tie rule.
+        {
+            const bool mine_ok = tid < N * H;
+            const int i = mine_ok ? tid % N : 0, h = mine_ok ? tid / N : 0;
+            const int jh = (N + H - 1) / H, jlo = h * jh, jhi = mine_ok ? min(N, jlo + jh) : jlo;
             const acc_t mine = qr_s[i];
+            const int imin = __reduce_min_sync(0xffffffffu, i), imax = __reduce_max_sync(0xffffffffu, i);
+            const bool high = p.tie == SVOC_TIE_HIGH_INDEX_KEPT;
             int rank = 0;
-            if (p.tie == SVOC_TIE_HIGH_INDEX_KEPT) {
-                for (int j = jlo; j < jhi; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j > i)) ? 1 : 0;
+            const int a_end = min(jhi, max(jlo, imin));        // [jlo, a_end): every j < i
+            const int b_beg = max(jlo, min(jhi, imax + 1));    // [b_beg, jhi): every j > i
+            if (high) {
+                for (int j = jlo; j < a_end; ++j) rank += qr_s[j] < mine ? 1 : 0;
+                for (int j = b_beg; j < jhi; ++j) rank += qr_s[j] <= mine ? 1 : 0;
+                for (int j = a_end; j < b_beg; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j > i)) ? 1 : 0;
             } else {
-                for (int j = jlo; j < jhi; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j < i)) ? 1 : 0;
+                for (int j = jlo; j < a_end; ++j) rank += qr_s[j] <= mine ? 1 : 0;
+                for (int j = b_beg; j < jhi; ++j) rank += qr_s[j] < mine ? 1 : 0;
+                for (int j = a_end; j < b_beg; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j < i)) ? 1 : 0;
             }
-            rankp[h * N + i] = rank;
+            if (mine_ok) rankp[h * N + i] = rank;
         }
         __syncthreads();
         {
@@ -565,7 +620,7 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
     s += al((size_t)H * N * 4);
     s += al((size_t)(P * RP / 32 + 1) * 4);
     s += 16;
-    s += al((size_t)D * 4) + 3 * al((size_t)D * es) + 3 * al((size_t)D * 4);
+    s += al((size_t)D * 4) + 5 * al((size_t)D * es) + 3 * al((size_t)D * 4);
     s += al((size_t)N);
     return s;
 }
