@@ -103,21 +103,27 @@ __device__ __forceinline__ unsigned wide_key(typename Tr::in_t x, typename Tr::i
     return x < lo ? 0u : (x > hi ? 126u : k);
 }
 
-template <class Tr, bool FIRST>
+template <class Tr, bool FIRST, int DT>
 __device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename Tr::in_t *tile, const uint8_t *keep,
                                                 typename Tr::in_t lo, typename Tr::in_t hi,
                                                 const typename WideKey<Tr>::Scale &sc) {
+    const int WD = DT ? DT : w.D;
     const int row_lo = w.part * w.RP;
-    const typename Tr::in_t *ptr = tile + row_lo * w.D + w.c;
+    const typename Tr::in_t *ptr = tile + row_lo * WD + w.c;
     for (int g = 0; g < w.RP; g += 16) {
         unsigned f[16];
+        if (!keep && row_lo + g + 16 <= w.N) {   // whole group valid: no per-row checks
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int row = row_lo + g + k;
-            f[k] = 127u;
-            if (row < w.N && (!keep || keep[row])) f[k] = wide_key<Tr, FIRST>(ptr[k * w.D], lo, hi, sc);
+            for (int k = 0; k < 16; ++k) f[k] = wide_key<Tr, FIRST>(ptr[k * WD], lo, hi, sc);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int row = row_lo + g + k;
+                f[k] = 127u;
+                if (row < w.N && (!keep || keep[row])) f[k] = wide_key<Tr, FIRST>(ptr[k * WD], lo, hi, sc);
+            }
         }
-        ptr += 16 * w.D;
+        ptr += 16 * WD;
         *reinterpret_cast<uint4 *>(w.mykeys + g) =
             make_uint4(pack4(f[0], f[1], f[2], f[3]), pack4(f[4], f[5], f[6], f[7]), pack4(f[8], f[9], f[10], f[11]),
                        pack4(f[12], f[13], f[14], f[15]));
@@ -126,7 +132,7 @@ __device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename
 
 // Centre of the flagged rows of every column (all rows when keep == nullptr).  Must be called by
 // all threads of the CTA (it synchronises); the result is valid in the part-0 thread of a column.
-template <class Tr>
+template <class Tr, int DT>
 __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, const typename Tr::in_t *tile,
                                                           const uint8_t *keep, int n_valid, int kind, bool col_const,
                                                           bool col_fallback, typename Tr::in_t const_value, int &buf,
@@ -134,13 +140,14 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using Key = WideKey<Tr>;
+    const int WD = DT ? DT : w.D;
     refined = false;
     val_t centre = 0;
     if (kind == SVOC_CENTRE_MEAN) {
         if (w.has_unit && w.part == 0) {
             val_t s = 0;
             for (int i = 0; i < w.N; ++i)
-                if (!keep || keep[i]) s += (val_t)tile[(size_t)i * w.D + w.c];
+                if (!keep || keep[i]) s += (val_t)tile[(size_t)i * WD + w.c];
             centre = Tr::mean(s, n_valid);
         }
         return centre;
@@ -162,11 +169,11 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
         int L = 0;
         for (int bit = 6; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
-            if (active) w.partial[(buf * w.P + w.part) * w.D + w.c] = (int)count_ge(w.mykeys, w.RP, cand);
+            if (active) w.partial[(buf * w.P + w.part) * WD + w.c] = (int)count_ge(w.mykeys, w.RP, cand);
             __syncthreads();
             if (active) {
                 int tot = 0;
-                for (int q = 0; q < w.P; ++q) tot += w.partial[(buf * w.P + q) * w.D + w.c];
+                for (int q = 0; q < w.P; ++q) tot += w.partial[(buf * w.P + q) * WD + w.c];
                 const int lt = slots - tot;  // sentinels (127) are never below a pivot
                 if (lt <= klo) { prefix = cand; L = lt; }
             }
@@ -192,12 +199,12 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                     const int pos = __ffs(acc) - 1;
                     acc &= acc - 1;
                     const int row = row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3);
-                    const in_t x = tile[row * w.D + w.c];
+                    const in_t x = tile[row * WD + w.c];
                     const uint32_t kx = okey(x);
                     kmin = kx < kmin ? kx : kmin;
                     kmax = kx > kmax ? kx : kmax;
                     const int slot = atomicAdd(&w.cand_cnt[w.c], 1);
-                    if (slot < WIDE_CAP) list[slot * w.D + w.c] = x;
+                    if (slot < WIDE_CAP) list[slot * WD + w.c] = x;
                 }
             }
             if (kmin <= kmax) {
@@ -216,20 +223,16 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                 if (w.part == 0) {
                     val_t sk, ku;
                     int stw = STW_OK;
-                    centre = column_centre_generic<Tr>(tile + w.c, w.D, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                    centre = column_centre_generic<Tr>(tile + w.c, WD, w.N, keep, n_valid, kind, false, sk, ku, stw);
                     have_centre = true;
                 }
             } else if (m <= WIDE_CAP) {
                 const in_t *lc = list + w.c;
                 for (int a = w.part; a < m; a += w.P) {
-                    const in_t v = lc[a * w.D];
-                    int below = 0, equal_before = 0;
-                    for (int b = 0; b < m; ++b) {
-                        const in_t u = lc[b * w.D];
-                        below += u < v ? 1 : 0;
-                        equal_before += (u == v && b < a) ? 1 : 0;
-                    }
-                    const int rk = below + equal_before;
+                    const in_t v = lc[a * WD];
+                    int rk = 0;
+                    for (int b = 0; b < a; ++b) rk += lc[b * WD] <= v ? 1 : 0;       // equal values: earlier slot first
+                    for (int b = a + 1; b < m; ++b) rk += lc[b * WD] < v ? 1 : 0;
                     if (rk == j1) res_lo[w.c] = v;
                     if (rk == j2) res_hi[w.c] = v;
                     if (rk == m - 1 && j2 >= m) thr[w.c] = v;   // window maximum, for the rescue scan
@@ -247,7 +250,7 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                 } else if (!Key::make(a, b, sc)) {
                     val_t sk, ku;
                     int stw = STW_OK;
-                    centre = column_centre_generic<Tr>(tile + w.c, w.D, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                    centre = column_centre_generic<Tr>(tile + w.c, WD, w.N, keep, n_valid, kind, false, sk, ku, stw);
                     have_centre = true;
                 } else {
                     flag = 2;
@@ -272,8 +275,8 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
         if (f == 1) {                          // minimum of the flagged rows above the window
             const in_t t0 = thr[w.c];
             uint32_t best = 0xffffffffu;
-            const in_t *ptr = tile + row_lo * w.D + w.c;
-            for (int row = row_lo; row < row_hi; ++row, ptr += w.D) {
+            const in_t *ptr = tile + row_lo * WD + w.c;
+            for (int row = row_lo; row < row_hi; ++row, ptr += WD) {
                 if (keep && !keep[row]) continue;
                 const in_t x = *ptr;
                 if (x > t0) { const uint32_t kx = okey(x); best = kx < best ? kx : best; }
@@ -283,7 +286,7 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
             const in_t a = rlo[w.c], b = rhi[w.c];
             typename Key::Scale sc;
             Key::make(a, b, sc);
-            wide_build_keys<Tr, false>(w, tile, keep, a, b, sc);
+            wide_build_keys<Tr, false, DT>(w, tile, keep, a, b, sc);
             refined = true;
         }
         const int more = __syncthreads_or(f == 2);
@@ -296,14 +299,14 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     return centre;
 }
 
-template <class Tr>
+template <class Tr, int DT>
 __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
     using Key = WideKey<Tr>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int N = p.N, D = p.D, R = p.R, P = p.wP, RP = p.wRP, CS = p.wCS, H = p.wH;
+    const int N = p.N, D = DT ? DT : p.D, R = p.R, P = p.wP, RP = p.wRP, CS = p.wCS, H = p.wH;
     const int tid = threadIdx.x;
     auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
 
@@ -409,7 +412,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
             typename Key::Scale sc;
             col_fb = !col_const && !Key::make(lo, hi, sc);
             if (!col_const && !col_fb) {
-                wide_build_keys<Tr, true>(w, tile, nullptr, lo, hi, sc);
+                wide_build_keys<Tr, true, DT>(w, tile, nullptr, lo, hi, sc);
             } else {
                 for (int g = 0; g < RP; g += 16) *reinterpret_cast<uint4 *>(w.mykeys + g) = make_uint4(0, 0, 0, 0);
             }
@@ -417,7 +420,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         }
         // ---- phase 1c: first-pass centre
         bool refined1 = false, refined2 = false;
-        const val_t e1 = wide_centre<Tr>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
+        const val_t e1 = wide_centre<Tr, DT>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
         if (w.has_unit && w.part == 0) {
             c1[w.c] = e1;
             if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * D + w.c] = e1;
@@ -485,13 +488,36 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
             int rank = 0;
             const int a_end = min(jhi, max(jlo, imin));        // [jlo, a_end): every j < i
             const int b_beg = max(jlo, min(jhi, imax + 1));    // [b_beg, jhi): every j > i
+            // one compare per pair; 128-bit broadcast loads where the range allows
+            auto count_lt = [&](int j0, int j1) {
+                int c = 0, j = j0;
+                if constexpr (sizeof(acc_t) == 4) {
+                    for (; j < j1 && (j & 3); ++j) c += qr_s[j] < mine ? 1 : 0;
+                    for (; j + 4 <= j1; j += 4) {
+                        const float4 v = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(qr_s) + j);
+                        c += (v.x < mine ? 1 : 0) + (v.y < mine ? 1 : 0) + (v.z < mine ? 1 : 0) + (v.w < mine ? 1 : 0);
+                    }
+                }
+                for (; j < j1; ++j) c += qr_s[j] < mine ? 1 : 0;
+                return c;
+            };
+            auto count_le = [&](int j0, int j1) {
+                int c = 0, j = j0;
+                if constexpr (sizeof(acc_t) == 4) {
+                    for (; j < j1 && (j & 3); ++j) c += qr_s[j] <= mine ? 1 : 0;
+                    for (; j + 4 <= j1; j += 4) {
+                        const float4 v = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(qr_s) + j);
+                        c += (v.x <= mine ? 1 : 0) + (v.y <= mine ? 1 : 0) + (v.z <= mine ? 1 : 0) + (v.w <= mine ? 1 : 0);
+                    }
+                }
+                for (; j < j1; ++j) c += qr_s[j] <= mine ? 1 : 0;
+                return c;
+            };
             if (high) {
-                for (int j = jlo; j < a_end; ++j) rank += qr_s[j] < mine ? 1 : 0;
-                for (int j = b_beg; j < jhi; ++j) rank += qr_s[j] <= mine ? 1 : 0;
+                rank = count_lt(jlo, a_end) + count_le(b_beg, jhi);
                 for (int j = a_end; j < b_beg; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j > i)) ? 1 : 0;
             } else {
-                for (int j = jlo; j < a_end; ++j) rank += qr_s[j] <= mine ? 1 : 0;
-                for (int j = b_beg; j < jhi; ++j) rank += qr_s[j] < mine ? 1 : 0;
+                rank = count_le(jlo, a_end) + count_lt(b_beg, jhi);
                 for (int j = a_end; j < b_beg; ++j) rank += (qr_s[j] < mine || (qr_s[j] == mine && j < i)) ? 1 : 0;
             }
             if (mine_ok) rankp[h * N + i] = rank;
@@ -560,7 +586,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         // refined keys behind, so the unit is re-keyed rather than patched)
         if (w.has_unit && !col_const && !col_fb) {
             if (refined1) {
-                wide_build_keys<Tr, true>(w, tile, keep_s, lo0, hi0, sc0);
+                wide_build_keys<Tr, true, DT>(w, tile, keep_s, lo0, hi0, sc0);
             } else {
                 for (int g = 0; g < RP; g += 32) {   // dropped rows of this unit -> sentinel key
                     const int base = row_lo + g;
@@ -576,7 +602,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         }
         // ---- phase 4: second-pass centre over the reliable rows (+ moments)
         val_t cons = 0;
-        if (!shape2) cons = wide_centre<Tr>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
+        if (!shape2) cons = wide_centre<Tr, DT>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
         if (w.has_unit && w.part == 0) {
             reinterpret_cast<val_t *>(p.consensus)[(size_t)r * D + w.c] = cons;
             if (p.want_moments) {
@@ -627,7 +653,10 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
 
 template <class Tr>
 int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
-    auto kern = consensus_wide_kernel<Tr>;
+    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0>;
+    if (p.D == 128) kern = consensus_wide_kernel<Tr, 128>;   // compile-time row stride: no address arithmetic
+    else if (p.D == 64) kern = consensus_wide_kernel<Tr, 64>;
+    else if (p.D == 32) kern = consensus_wide_kernel<Tr, 32>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, WIDE_THREADS, pl.smem, st>>>(p);
