@@ -55,6 +55,25 @@ __device__ __forceinline__ float vmax(float a, float b) { return fmaxf(a, b); }
 __device__ __forceinline__ int32_t vmin(int32_t a, int32_t b) { return min(a, b); }
 __device__ __forceinline__ int32_t vmax(int32_t a, int32_t b) { return max(a, b); }
 
+// barrier among the threads that share this unit's columns
+__device__ __forceinline__ void unit_sync(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ int unit_sync_or(int id, int count, int pred) {
+    int r;
+    asm volatile(
+        "{\n"
+        ".reg .pred p, q;\n"
+        "setp.ne.s32 p, %1, 0;\n"
+        "barrier.red.or.pred q, %2, %3, p;\n"
+        "selp.s32 %0, 1, 0, q;\n"
+        "}\n"
+        : "=r"(r)
+        : "r"(pred), "r"(id), "r"(count)
+        : "memory");
+    return r;
+}
+
 __device__ __forceinline__ unsigned pack4(unsigned a, unsigned b, unsigned c, unsigned d) {
     return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
 }
@@ -88,7 +107,9 @@ struct WideCtx {
     void *list;         // [WIDE_CAP][D] in_t
     int *flag;          // [D] 0 resolved, 1 needs the minimum above `thr`, 2 needs a finer re-keying
     void *thr, *rlo, *rhi;          // [D] in_t each
-    void *res_lo, *res_hi;          // [D] in_t: the two order statistics found by the rank phase
+    int *best;                      // [3][D] packed (rank << 8 | slot) maxima: lower, upper statistic, window maximum
+    int bar_id, bar_count;          // barrier of this unit's slab (32 columns x P parts), or the CTA barrier
+    bool slab;                      // slab mode: threads without a unit skip the selection entirely
     uint32_t *wmin, *wmax, *resc;   // [D] order-preserving keys: window min / max, rescue minimum
 };
 
@@ -132,7 +153,7 @@ __device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename
 
 // Centre of the flagged rows of every column (all rows when keep == nullptr).  Must be called by
 // all threads of the CTA (it synchronises); the result is valid in the part-0 thread of a column.
-template <class Tr, int DT>
+template <class Tr, int DT, int PT>
 __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, const typename Tr::in_t *tile,
                                                           const uint8_t *keep, int n_valid, int kind, bool col_const,
                                                           bool col_fallback, typename Tr::in_t const_value, int &buf,
@@ -141,23 +162,30 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     using val_t = typename Tr::val_t;
     using Key = WideKey<Tr>;
     const int WD = DT ? DT : w.D;
+    const int WP = PT ? PT : w.P;
     refined = false;
     val_t centre = 0;
     if (kind == SVOC_CENTRE_MEAN) {
         if (w.has_unit && w.part == 0) {
             val_t s = 0;
             for (int i = 0; i < w.N; ++i)
-                if (!keep || keep[i]) s += (val_t)tile[(size_t)i * WD + w.c];
+                if (!keep || keep[i]) s += (val_t)tile[i * WD + w.c];
             centre = Tr::mean(s, n_valid);
         }
         return centre;
     }
+    if (w.slab && !w.has_unit) return centre;   // not a member of any slab barrier
     int klo, khi;
     centre_ranks(kind, n_valid, klo, khi);
     in_t *list = reinterpret_cast<in_t *>(w.list);
     in_t *thr = reinterpret_cast<in_t *>(w.thr), *rlo = reinterpret_cast<in_t *>(w.rlo), *rhi = reinterpret_cast<in_t *>(w.rhi);
-    const int slots = w.P * w.RP;
+    const int slots = WP * w.RP;
     const int row_lo = w.part * w.RP, row_hi = min(w.N, row_lo + w.RP);
+    const int pstride = WP * WD;                        // one buffer of partial counts
+    int *my_partial = w.partial + w.part * WD + w.c;
+    const int *col_partial = w.partial + w.c;
+    int *best1 = w.best + w.c, *best2 = w.best + WD + w.c, *best3 = w.best + 2 * WD + w.c;
+    const in_t *lc = list + w.c;
     bool done = !w.has_unit || col_const;
     in_t v_lo = const_value, v_hi = const_value;
     bool have_centre = false;
@@ -167,13 +195,15 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
         // ---- bisection over the 7 key bits for rank klo
         unsigned prefix = 0;
         int L = 0;
+#pragma unroll
         for (int bit = 6; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
-            if (active) w.partial[(buf * w.P + w.part) * WD + w.c] = (int)count_ge(w.mykeys, w.RP, cand);
-            __syncthreads();
+            if (active) my_partial[buf * pstride] = (int)count_ge(w.mykeys, w.RP, cand);
+            unit_sync(w.bar_id, w.bar_count);
             if (active) {
                 int tot = 0;
-                for (int q = 0; q < w.P; ++q) tot += w.partial[(buf * w.P + q) * WD + w.c];
+#pragma unroll
+                for (int q = 0; q < WP; ++q) tot += col_partial[buf * pstride + q * WD];
                 const int lt = slots - tot;  // sentinels (127) are never below a pivot
                 if (lt <= klo) { prefix = cand; L = lt; }
             }
@@ -212,40 +242,54 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                 atomicMax(&w.wmax[w.c], kmax);
             }
         }
-        __syncthreads();
-        // ---- the two order statistics: the P threads of a column rank the window's rows between them
+        unit_sync(w.bar_id, w.bar_count);
+        // ---- rank the window's rows: the P threads of a column take every P-th slot, four at a time.
+        //      lt(v) = #{u < v}; the value of rank j is the candidate with the largest lt <= j.
         int flag = 0;
-        in_t *res_lo = reinterpret_cast<in_t *>(w.res_lo), *res_hi = reinterpret_cast<in_t *>(w.res_hi);
-        if (active) {
-            const int m = w.cand_cnt[w.c];   // rows in the window (not capped)
-            const int j1 = klo - L, j2 = khi - L;
+        const int m = active ? w.cand_cnt[w.c] : 0;   // rows in the window (not capped)
+        const int j1 = klo - L, j2 = khi - L;
+        const bool rankable = active && !col_fallback && m <= WIDE_CAP;
+        if (rankable) {
+            for (int base = w.part; base < m; base += 4 * WP) {
+                const int a0 = base, a1 = base + WP, a2 = base + 2 * WP, a3 = base + 3 * WP;
+                const in_t v0 = lc[a0 * WD];
+                const in_t v1 = a1 < m ? lc[a1 * WD] : v0, v2 = a2 < m ? lc[a2 * WD] : v0, v3 = a3 < m ? lc[a3 * WD] : v0;
+                int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+#pragma unroll 2
+                for (int b = 0; b < m; ++b) {
+                    const in_t u = lc[b * WD];
+                    r0 += u < v0 ? 1 : 0;
+                    r1 += u < v1 ? 1 : 0;
+                    r2 += u < v2 ? 1 : 0;
+                    r3 += u < v3 ? 1 : 0;
+                }
+                auto publish = [&](int rk, int slot) {
+                    if (rk <= j1) atomicMax(best1, (rk << 8) | slot);
+                    if (rk <= j2) atomicMax(best2, (rk << 8) | slot);
+                    if (j2 >= m) atomicMax(best3, (rk << 8) | slot);
+                };
+                publish(r0, a0);
+                if (a1 < m) publish(r1, a1);
+                if (a2 < m) publish(r2, a2);
+                if (a3 < m) publish(r3, a3);
+            }
+            if (j2 >= m) flag = 1;
+        } else if (active && w.part == 0) {
             if (col_fallback) {
-                if (w.part == 0) {
-                    val_t sk, ku;
-                    int stw = STW_OK;
-                    centre = column_centre_generic<Tr>(tile + w.c, WD, w.N, keep, n_valid, kind, false, sk, ku, stw);
-                    have_centre = true;
-                }
-            } else if (m <= WIDE_CAP) {
-                const in_t *lc = list + w.c;
-                for (int a = w.part; a < m; a += w.P) {
-                    const in_t v = lc[a * WD];
-                    int rk = 0;
-                    for (int b = 0; b < a; ++b) rk += lc[b * WD] <= v ? 1 : 0;       // equal values: earlier slot first
-                    for (int b = a + 1; b < m; ++b) rk += lc[b * WD] < v ? 1 : 0;
-                    if (rk == j1) res_lo[w.c] = v;
-                    if (rk == j2) res_hi[w.c] = v;
-                    if (rk == m - 1 && j2 >= m) thr[w.c] = v;   // window maximum, for the rescue scan
-                }
-                if (j2 >= m) flag = 1;
-            } else if (w.part == 0) {
+                val_t sk, ku;
+                int stw = STW_OK;
+                centre = column_centre_generic<Tr>(tile + w.c, WD, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                have_centre = true;
+            } else {
                 in_t a, b;
                 unkey(w.wmin[w.c], a);
                 unkey(w.wmax[w.c], b);
                 typename Key::Scale sc;
                 if (!(b > a)) {              // the whole window is one value
-                    res_lo[w.c] = a;
-                    res_hi[w.c] = a;
+                    v_lo = a;
+                    v_hi = a;
+                    have_centre = j2 < m;
+                    centre = Tr::half_sum((val_t)a, (val_t)a);
                     if (j2 >= m) { flag = 1; thr[w.c] = a; }
                 } else if (!Key::make(a, b, sc)) {
                     val_t sk, ku;
@@ -258,19 +302,27 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                     rhi[w.c] = b;
                 }
             }
-            if (w.part == 0) {
-                w.flag[w.c] = flag;
-                w.wmin[w.c] = 0xffffffffu;
-                w.wmax[w.c] = 0u;
-                w.resc[w.c] = 0xffffffffu;
-            }
         }
-        const int any = __syncthreads_or(flag);
+        if (active && w.part == 0) {
+            w.flag[w.c] = flag;
+            w.wmin[w.c] = 0xffffffffu;
+            w.wmax[w.c] = 0u;
+            w.resc[w.c] = 0xffffffffu;
+        }
+        const int any = unit_sync_or(w.bar_id, w.bar_count, flag);
         if (active && w.part == 0) {
             w.cand_cnt[w.c] = 0;   // everyone has read it; the next collect comes after more barriers
-            if (!have_centre) { v_lo = res_lo[w.c]; v_hi = res_hi[w.c]; }
+            if (rankable) {
+                v_lo = lc[(*best1 & 0xff) * WD];
+                if (j2 < m) v_hi = lc[(*best2 & 0xff) * WD];
+                else thr[w.c] = lc[(*best3 & 0xff) * WD];
+                *best1 = -1;
+                *best2 = -1;
+                *best3 = -1;
+            }
         }
         if (!any) break;            // common case: every column resolved
+        unit_sync(w.bar_id, w.bar_count);   // thr / ranges written by the part-0 threads are visible
         const int f = active ? w.flag[w.c] : 0;
         if (f == 1) {                          // minimum of the flagged rows above the window
             const in_t t0 = thr[w.c];
@@ -289,9 +341,8 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
             wide_build_keys<Tr, false, DT>(w, tile, keep, a, b, sc);
             refined = true;
         }
-        const int more = __syncthreads_or(f == 2);
+        const int more = unit_sync_or(w.bar_id, w.bar_count, f == 2);
         if (f == 1 && w.part == 0) unkey(w.resc[w.c], v_hi);
-        if (f == 2 && w.part == 0) { v_lo = const_value; v_hi = const_value; }
         if (f != 2) done = true;
         if (!more) break;
     }
@@ -299,14 +350,14 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     return centre;
 }
 
-template <class Tr, int DT>
+template <class Tr, int DT, int PT>
 __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
     using Key = WideKey<Tr>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int N = p.N, D = DT ? DT : p.D, R = p.R, P = p.wP, RP = p.wRP, CS = p.wCS, H = p.wH;
+    const int N = p.N, D = DT ? DT : p.D, R = p.R, P = PT ? PT : p.wP, RP = p.wRP, CS = p.wCS, H = p.wH;
     const int tid = threadIdx.x;
     auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
 
@@ -332,8 +383,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
     uint32_t *wmin_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
     uint32_t *wmax_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
     uint32_t *resc_s = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)D * 4);
-    in_t *reslo_s = reinterpret_cast<in_t *>(smem_raw + off);   off += al((size_t)D * sizeof(in_t));
-    in_t *reshi_s = reinterpret_cast<in_t *>(smem_raw + off);   off += al((size_t)D * sizeof(in_t));
+    int *best_s = reinterpret_cast<int *>(smem_raw + off);      off += al((size_t)3 * D * 4);
     uint8_t *keep_s = smem_raw + off;
 
     WideCtx w;
@@ -347,7 +397,11 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
     w.list = list;
     w.flag = flag_s; w.thr = thr_s; w.rlo = rlo_s; w.rhi = rhi_s;
     w.wmin = wmin_s; w.wmax = wmax_s; w.resc = resc_s;
-    w.res_lo = reslo_s; w.res_hi = reshi_s;
+    w.best = best_s;
+    // slab mode: the P warps that own the same 32 columns synchronise among themselves
+    w.slab = (D % 32 == 0) && (D / 32 <= 15);
+    w.bar_id = w.slab ? 1 + (w.c >> 5) : 0;
+    w.bar_count = w.slab ? 32 * P : WIDE_THREADS;
 
     const size_t round_elems = (size_t)N * D;
     const uint32_t round_bytes = (uint32_t)(round_elems * sizeof(in_t));
@@ -358,6 +412,9 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         wmax_s[k] = 0u;
         resc_s[k] = 0xffffffffu;
         flag_s[k] = 0;
+        best_s[k] = -1;
+        best_s[D + k] = -1;
+        best_s[2 * D + k] = -1;
     }
     __syncthreads();
     uint32_t parity = 0;
@@ -420,7 +477,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         }
         // ---- phase 1c: first-pass centre
         bool refined1 = false, refined2 = false;
-        const val_t e1 = wide_centre<Tr, DT>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
+        const val_t e1 = wide_centre<Tr, DT, PT>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
         if (w.has_unit && w.part == 0) {
             c1[w.c] = e1;
             if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * D + w.c] = e1;
@@ -602,7 +659,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
         }
         // ---- phase 4: second-pass centre over the reliable rows (+ moments)
         val_t cons = 0;
-        if (!shape2) cons = wide_centre<Tr, DT>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
+        if (!shape2) cons = wide_centre<Tr, DT, PT>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
         if (w.has_unit && w.part == 0) {
             reinterpret_cast<val_t *>(p.consensus)[(size_t)r * D + w.c] = cons;
             if (p.want_moments) {
@@ -646,17 +703,18 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
     s += al((size_t)H * N * 4);
     s += al((size_t)(P * RP / 32 + 1) * 4);
     s += 16;
-    s += al((size_t)D * 4) + 5 * al((size_t)D * es) + 3 * al((size_t)D * 4);
+    s += al((size_t)D * 4) + 3 * al((size_t)D * es) + 3 * al((size_t)D * 4) + al((size_t)3 * D * 4);
     s += al((size_t)N);
     return s;
 }
 
 template <class Tr>
 int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
-    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0>;
-    if (p.D == 128) kern = consensus_wide_kernel<Tr, 128>;   // compile-time row stride: no address arithmetic
-    else if (p.D == 64) kern = consensus_wide_kernel<Tr, 64>;
-    else if (p.D == 32) kern = consensus_wide_kernel<Tr, 32>;
+    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0>;
+    // compile-time row stride and part count for the common shapes: no address arithmetic
+    if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4>;
+    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8>;
+    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, WIDE_THREADS, pl.smem, st>>>(p);
