@@ -78,23 +78,39 @@ __device__ __forceinline__ unsigned pack4(unsigned a, unsigned b, unsigned c, un
     return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
 }
 
-// number of keys >= cand among `rp` packed byte keys (rp multiple of 32, keys <= 127, 1 <= cand <= 127)
-__device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp, unsigned cand) {
-    const unsigned cb = (128u - cand) * 0x01010101u;
+// Counting "key >= cand" over packed byte keys (rp multiple of 32, keys <= 127, 1 <= cand <= 127).
+// y = key + (128 - cand) sets the byte MSB exactly when key >= cand and never carries.  Summing the
+// bytes of y as SIGNED values subtracts 256 for every set MSB, so with the plain byte sum known
+//     #(key >= cand) = (sum_keys + rp * (128 - cand) - signed_sum(y)) / 256
+// which costs one add and one IDP.4A per four keys.
+__device__ __forceinline__ int key_byte_sum(const uint8_t *keys, int rp) {
     unsigned acc = 0;
+    for (int g = 0; g < rp; g += 16) {
+        const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
+        acc = __dp4a(a.x, 0x01010101u, acc);
+        acc = __dp4a(a.y, 0x01010101u, acc);
+        acc = __dp4a(a.z, 0x01010101u, acc);
+        acc = __dp4a(a.w, 0x01010101u, acc);
+    }
+    return (int)acc;
+}
+
+__device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp, unsigned cand, int sum_keys) {
+    const unsigned cb = (128u - cand) * 0x01010101u;
+    int acc0 = 0, acc1 = 0;
     for (int g = 0; g < rp; g += 32) {
         const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
         const uint4 b = *reinterpret_cast<const uint4 *>(keys + g + 16);
-        acc = __dp4a((a.x + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((a.y + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((a.z + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((a.w + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((b.x + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((b.y + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((b.z + cb) & 0x80808080u, 0x01010101u, acc);
-        acc = __dp4a((b.w + cb) & 0x80808080u, 0x01010101u, acc);
+        acc0 = __dp4a((int)(a.x + cb), 0x01010101, acc0);
+        acc1 = __dp4a((int)(a.y + cb), 0x01010101, acc1);
+        acc0 = __dp4a((int)(a.z + cb), 0x01010101, acc0);
+        acc1 = __dp4a((int)(a.w + cb), 0x01010101, acc1);
+        acc0 = __dp4a((int)(b.x + cb), 0x01010101, acc0);
+        acc1 = __dp4a((int)(b.y + cb), 0x01010101, acc1);
+        acc0 = __dp4a((int)(b.z + cb), 0x01010101, acc0);
+        acc1 = __dp4a((int)(b.w + cb), 0x01010101, acc1);
     }
-    return acc >> 7;
+    return (unsigned)(sum_keys + rp * (int)(128u - cand) - (acc0 + acc1)) >> 8;
 }
 
 struct WideCtx {
@@ -194,11 +210,12 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
         const bool active = !done;
         // ---- bisection over the 7 key bits for rank klo
         unsigned prefix = 0;
-        int L = 0;
+        int L = 0, LE = n_valid;
+        const int sum_keys = active ? key_byte_sum(w.mykeys, w.RP) : 0;
 #pragma unroll
         for (int bit = 6; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
-            if (active) my_partial[buf * pstride] = (int)count_ge(w.mykeys, w.RP, cand);
+            if (active) my_partial[buf * pstride] = (int)count_ge(w.mykeys, w.RP, cand, sum_keys);
             unit_sync(w.bar_id, w.bar_count);
             if (active) {
                 int tot = 0;
@@ -206,12 +223,15 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
                 for (int q = 0; q < WP; ++q) tot += col_partial[buf * pstride + q * WD];
                 const int lt = slots - tot;  // sentinels (127) are never below a pivot
                 if (lt <= klo) { prefix = cand; L = lt; }
+                else LE = lt;    // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
             }
             buf ^= 1;
         }
-        // ---- collect the rows whose key lies in the window [prefix, prefix + 3)
+        // ---- collect the rows whose key lies in the window: the bucket of rank klo alone when rank khi
+        //      is inside it too, else that bucket and the next two
         if (active) {
-            const unsigned up = prefix + 3 > 127u ? 127u : prefix + 3;
+            const unsigned span = (khi < LE) ? 1u : 3u;
+            const unsigned up = prefix + span > 127u ? 127u : prefix + span;
             const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
             uint32_t kmin = 0xffffffffu, kmax = 0u;
             for (int g = 0; g < w.RP; g += 32) {
@@ -350,8 +370,8 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     return centre;
 }
 
-template <class Tr, int DT, int PT>
-__global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const Params p) {
+template <class Tr, int DT, int PT, int NT>
+__global__ void __launch_bounds__(NT, 1) consensus_wide_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
@@ -401,12 +421,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
     // slab mode: the P warps that own the same 32 columns synchronise among themselves
     w.slab = (D % 32 == 0) && (D / 32 <= 15);
     w.bar_id = w.slab ? 1 + (w.c >> 5) : 0;
-    w.bar_count = w.slab ? 32 * P : WIDE_THREADS;
+    w.bar_count = w.slab ? 32 * P : NT;
 
     const size_t round_elems = (size_t)N * D;
     const uint32_t round_bytes = (uint32_t)(round_elems * sizeof(in_t));
     if (tid == 0) mbar_init(bar, 1);
-    for (int k = tid; k < D; k += WIDE_THREADS) {
+    for (int k = tid; k < D; k += NT) {
         cand_cnt[k] = 0;
         wmin_s[k] = 0xffffffffu;
         wmax_s[k] = 0u;
@@ -434,7 +454,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 1) consensus_wide_kernel(const P
             mbar_wait(bar, parity);
             parity ^= 1;
         } else {
-            for (size_t e = tid; e < round_elems; e += WIDE_THREADS) tile[e] = gsrc[e];
+            for (size_t e = tid; e < round_elems; e += NT) tile[e] = gsrc[e];
         }
         if (tid == 0) *stw_s = STW_OK;
         __syncthreads();
@@ -710,14 +730,15 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
 
 template <class Tr>
 int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
-    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0>;
+    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0, WIDE_THREADS>;
     // compile-time row stride and part count for the common shapes: no address arithmetic
-    if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4>;
-    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8>;
-    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8>;
+    if (pl.threads == 1024) kern = consensus_wide_kernel<Tr, 128, 8, 1024>;
+    else if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS>;
+    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8, WIDE_THREADS>;
+    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8, WIDE_THREADS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
-    kern<<<(unsigned)pl.grid, WIDE_THREADS, pl.smem, st>>>(p);
+    kern<<<(unsigned)pl.grid, pl.threads, pl.smem, st>>>(p);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
     count_launch();

@@ -6,6 +6,7 @@
 #include <string>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "consensus_wide.cuh"
 
@@ -54,20 +55,23 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
     if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
     if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
+    // 1024 threads (8 warps per scheduler) for the 128-dimension shape when the environment asks for it
+    static const bool big = [] { const char *e = getenv("SVOC_WIDE_1024"); return e && e[0] == '1'; }();
+    const int NT = (big && D == 128 && N >= 256) ? 1024 : 512;
     int P = 1;
-    while (P * 2 <= 8 && P * 2 * D <= 512 && P * 2 * 32 <= N) P *= 2;
+    while (P * 2 <= 8 && P * 2 * D <= NT && P * 2 * 32 <= N) P *= 2;
     const int RP = (((N + P - 1) / P) + 31) & ~31;
     if (P * RP > 512) return false;
     int CS = P * RP;
     while ((CS / 4) % 32 != 4) CS += 16;
     int H = 1;
-    while (H * 2 * N <= 512 && H * 2 <= D) H *= 2;
+    while (H * 2 * N <= NT && H * 2 <= D) H *= 2;
     const size_t smem = wide_smem_bytes(N, D, P, RP, CS, H, 4, c.dtype == SVOC_F32 ? 4 : 8);
     if (smem > 227 * 1024) return false;
     pl.variant = 1;
     pl.wP = P; pl.wRP = RP; pl.wCS = CS; pl.wH = H;
     pl.smem = smem;
-    pl.threads = 512;
+    pl.threads = NT;
     pl.rb = 1;
     pl.npad = 0;
     pl.tile_smem = 1;
