@@ -87,6 +87,9 @@ typedef struct svoc_outputs {
     void *skew;         /* [T][D] get_skewness(), contract.cairo:643-655 */
     void *kurt;         /* [T][D] get_kurtosis() */
     int32_t *status;    /* [T]    SVOC_ST_* */
+    int32_t *rank;      /* [T][N] position of every oracle in the selection order (0 = smallest qr, ties by
+                           tie_rule) — `ordered_oracles`, contract.cairo:469; N-1-rank is `rank_array`'s
+                           second return value (ipynb beta :342-352) */
 } svoc_outputs;
 
 /* Fixed-point ("wsad", value * 1e6 as signed integer) form — bit-exact restatement of
@@ -116,6 +119,11 @@ int svoc_consensus_float_host(const svoc_config *cfg, const void *pred, int64_t 
  * ipynb beta :260-267.  pred is [T][n_values] float64 on the device; out is [T] float64. */
 int svoc_expected_reliability(const double *pred, int64_t n_arrays, int32_t n_values, double *out,
                               void *stream);
+
+/* `rank_array` (ipynb beta :342-352 == client/oracle_scheduler.py:94-104) for T independent lists of n
+ * float64 values on the device: ranks[t][i] = n - 1 - (position of value i in a stable ascending sort),
+ * i.e. the largest value gets rank 0. */
+int svoc_rank_array(const double *values, int64_t n_lists, int32_t n, int32_t *ranks, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Synthetic workloads — the notebook generators on a counter-based Philox4x32-10 stream:

@@ -37,6 +37,7 @@ struct Params {
     uint32_t *reliable;
     void *consensus, *rel2, *skew, *kurt;
     int32_t *status;
+    int32_t *rank;
     int rb;          // rounds per CTA
     int words;       // ceil(N/32)
     int tile_smem;   // 1: rounds staged in shared memory; 0: read from global
@@ -360,6 +361,7 @@ __global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) consensus_kernel(const 
             for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j < i)) ? 1 : 0;
         }
         keep_s[w] = rank < R ? 1 : 0;
+        if (p.rank) p.rank[(size_t)r0 * N + w] = rank;
     }
     __syncthreads();
 

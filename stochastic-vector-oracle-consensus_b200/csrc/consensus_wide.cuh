@@ -609,6 +609,7 @@ __global__ void __launch_bounds__(NT, 1) consensus_wide_kernel(const Params p) {
                 for (int h = 0; h < H; ++h) rank += rankp[h * N + tid];
                 keepme = rank < R;
                 keep_s[tid] = keepme ? 1 : 0;
+                if (p.rank) p.rank[(size_t)r * N + tid] = rank;
             }
             if (tid < slots || tid < ((N + 31) & ~31)) {
                 const unsigned bits = __ballot_sync(0xffffffffu, keepme);

@@ -142,6 +142,7 @@ static Params make_params(const svoc_config &c, const void *pred, int64_t T, con
     p.skew = o.skew;
     p.kurt = o.kurt;
     p.status = o.status;
+    p.rank = o.rank;
     p.rb = pl.rb;
     p.words = (c.n_oracles + 31) / 32;
     p.tile_smem = pl.tile_smem;

@@ -1,4 +1,5 @@
 // svoc_aux.cu — small float helpers of the notebook that sit beside the consensus round.
+#include <algorithm>
 #include <string>
 
 #include "svoc_common.cuh"
@@ -36,7 +37,36 @@ __global__ void __launch_bounds__(128) expected_reliability_kernel(const double 
     for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if (lane == 0) out[w] = 1.0 - 2.0 * (s / (double)n);
 }
+
+// rank_array (ipynb beta :342-352): stable ascending position by counting, reversed.
+__global__ void __launch_bounds__(128) rank_array_kernel(const double *__restrict__ v, i64 n_lists, int n,
+                                                         int32_t *__restrict__ ranks) {
+    const i64 total = n_lists * n;
+    for (i64 e = (i64)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (i64)gridDim.x * blockDim.x) {
+        const i64 t = e / n;
+        const int i = (int)(e - t * n);
+        const double *x = v + (size_t)t * n;
+        const double mine = x[i];
+        int pos = 0;
+        for (int j = 0; j < n; ++j) pos += (x[j] < mine || (x[j] == mine && j < i)) ? 1 : 0;
+        ranks[e] = n - 1 - pos;
+    }
+}
 }  // namespace svoc
+
+extern "C" int svoc_rank_array(const double *values, int64_t n_lists, int32_t n, int32_t *ranks, void *stream) {
+    using namespace svoc;
+    if (n_lists < 0 || n < 1) return fail("bad sizes");
+    if (n_lists == 0) return 0;
+    if (!values || !ranks) return fail("null pointer");
+    const i64 total = n_lists * n;
+    const unsigned grid = (unsigned)std::min<i64>((total + 127) / 128, 148 * 16);
+    rank_array_kernel<<<grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(values, n_lists, n, ranks);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
+    count_launch();
+    return 0;
+}
 
 extern "C" int svoc_expected_reliability(const double *pred, int64_t n_arrays, int32_t n_values, double *out,
                                          void *stream) {

@@ -36,7 +36,7 @@ HostWorkspace g_ws[16];
 size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct ChunkLayout {
-    size_t in, essence1, qr, rel1, reliable, consensus, rel2, skew, kurt, status, total;
+    size_t in, essence1, qr, rel1, reliable, consensus, rel2, skew, kurt, status, rank, total;
 };
 
 ChunkLayout layout(const svoc_config &c, const svoc_outputs &o, int64_t rounds, size_t es, size_t vs) {
@@ -54,6 +54,7 @@ ChunkLayout layout(const svoc_config &c, const svoc_outputs &o, int64_t rounds, 
     L.skew = take(o.skew ? T * D * vs : 0);
     L.kurt = take(o.kurt ? T * D * vs : 0);
     L.status = take(T * 4);
+    L.rank = take(o.rank ? T * N * 4 : 0);
     L.total = off;
     return L;
 }
@@ -113,6 +114,7 @@ int consensus_host(const svoc_config *cfg, const void *pred, int64_t T, const sv
         d.skew = out->skew ? b + L.skew : nullptr;
         d.kurt = out->kurt ? b + L.kurt : nullptr;
         d.status = reinterpret_cast<int32_t *>(b + L.status);
+        d.rank = out->rank ? reinterpret_cast<int32_t *>(b + L.rank) : nullptr;
         if (int rc = consensus_device(cfg, b + L.in, n, &d, st, fixed)) return rc;
         auto back = [&](void *host, size_t at, size_t per_round) -> cudaError_t {
             if (!host) return cudaSuccess;
@@ -128,6 +130,7 @@ int consensus_host(const svoc_config *cfg, const void *pred, int64_t T, const sv
         CK(back(out->skew, L.skew, D * vs));
         CK(back(out->kurt, L.kurt, D * vs));
         CK(back(out->status, L.status, 4));
+        CK(back(out->rank, L.rank, N * 4));
     }
     CK(cudaStreamSynchronize(ws.st[0]));
     CK(cudaStreamSynchronize(ws.st[1]));

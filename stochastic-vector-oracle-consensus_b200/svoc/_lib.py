@@ -40,7 +40,7 @@ class SvocOutputs(C.Structure):
     _fields_ = [
         ("essence1", C.c_void_p), ("qr", C.c_void_p), ("rel1", C.c_void_p), ("reliable", C.c_void_p),
         ("consensus", C.c_void_p), ("rel2", C.c_void_p), ("skew", C.c_void_p), ("kurt", C.c_void_p),
-        ("status", C.c_void_p),
+        ("status", C.c_void_p), ("rank", C.c_void_p),
     ]
 
 
@@ -64,6 +64,7 @@ SYMBOLS = {
     "svoc_consensus_fixed_host": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
     "svoc_consensus_float_host": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
     "svoc_expected_reliability": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "svoc_rank_array": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "svoc_generate": (C.c_int, [C.POINTER(SvocGenConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "svoc_accumulate_stats": (C.c_int, [C.POINTER(SvocConfig), C.c_int64, C.POINTER(SvocOutputs), C.c_void_p, C.c_void_p, C.c_void_p]),
     "svoc_last_error": (C.c_char_p, []),

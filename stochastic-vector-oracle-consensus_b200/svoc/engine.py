@@ -37,6 +37,7 @@ class ConsensusResult:
     qr: Optional[torch.Tensor]              # [T, N]  per-oracle quadratic risk
     skew: Optional[torch.Tensor]            # [T, D]
     kurt: Optional[torch.Tensor]            # [T, D]
+    rank: Optional[torch.Tensor] = None     # [T, N] int32 position in the selection order (0 = smallest qr)
     n_oracles: int = 0
 
     @property
@@ -56,7 +57,7 @@ def make_config(n, d, n_failing, dtype, constrained=True, max_spread=0, centre=C
                       want_moments=int(bool(want_moments)), reserved=0)
 
 
-def _alloc_outputs(T, N, D, val_dtype, device, want_moments, want_qr, want_essence, pin=False):
+def _alloc_outputs(T, N, D, val_dtype, device, want_moments, want_qr, want_essence, pin=False, want_rank=False):
     kw = dict(device=device)
     if pin:
         kw["pin_memory"] = True
@@ -65,16 +66,17 @@ def _alloc_outputs(T, N, D, val_dtype, device, want_moments, want_qr, want_essen
         consensus=e(T, D), rel1=e(T), rel2=e(T), status=e(T, dt=torch.int32),
         reliable_words=e(T, (N + 31) // 32, dt=torch.int32),
         essence1=e(T, D) if want_essence else None, qr=e(T, N) if want_qr else None,
-        skew=e(T, D) if want_moments else None, kurt=e(T, D) if want_moments else None, n_oracles=N)
+        skew=e(T, D) if want_moments else None, kurt=e(T, D) if want_moments else None,
+        rank=e(T, N, dt=torch.int32) if want_rank else None, n_oracles=N)
     ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else None  # noqa: E731
     outs = SvocOutputs(essence1=ptr(res.essence1), qr=ptr(res.qr), rel1=ptr(res.rel1), reliable=ptr(res.reliable_words),
                        consensus=ptr(res.consensus), rel2=ptr(res.rel2), skew=ptr(res.skew), kurt=ptr(res.kurt),
-                       status=ptr(res.status))
+                       status=ptr(res.status), rank=ptr(res.rank))
     return res, outs
 
 
 def _run(pred: torch.Tensor, fixed: bool, host: bool, n_failing, constrained, max_spread, centre, centre2, tie_rule,
-         want_moments, want_qr, want_essence) -> ConsensusResult:
+         want_moments, want_qr, want_essence, want_rank=False) -> ConsensusResult:
     if pred.dim() != 3:
         raise ValueError("predictions must be [T, N, D]")
     if pred.dtype not in _DTYPES:
@@ -90,7 +92,7 @@ def _run(pred: torch.Tensor, fixed: bool, host: bool, n_failing, constrained, ma
     cfg = make_config(N, D, n_failing, dt, constrained, max_spread, centre, centre2, tie_rule, want_moments)
     val_dtype = torch.int64 if fixed else pred.dtype
     res, outs = _alloc_outputs(T, N, D, val_dtype, pred.device, want_moments, want_qr, want_essence,
-                               pin=host and pred.is_pinned())
+                               pin=host and pred.is_pinned(), want_rank=want_rank)
     if T == 0:
         return res
     if host:
@@ -106,18 +108,18 @@ def _run(pred: torch.Tensor, fixed: bool, host: bool, n_failing, constrained, ma
 
 def consensus_fixed(pred, n_failing, constrained=True, max_spread=0, centre=CENTRE_SMOOTH_MEDIAN_CAIRO,
                     centre2=CENTRE_DEFAULT, tie_rule=TIE_HIGH_INDEX_KEPT, want_moments=True, want_qr=True,
-                    want_essence=True) -> ConsensusResult:
+                    want_essence=True, want_rank=False) -> ConsensusResult:
     """T rounds of update_{un,}constrained_consensus on wsad integers (CUDA tensor in, CUDA tensors out)."""
     return _run(pred, True, False, n_failing, constrained, max_spread, centre, centre2, tie_rule, want_moments,
-                want_qr, want_essence)
+                want_qr, want_essence, want_rank)
 
 
 def consensus_float(pred, n_failing, constrained=True, max_spread=0.0, centre=CENTRE_SMOOTH_MEDIAN_CAIRO,
                     centre2=CENTRE_DEFAULT, tie_rule=TIE_HIGH_INDEX_KEPT, want_moments=False, want_qr=True,
-                    want_essence=True) -> ConsensusResult:
+                    want_essence=True, want_rank=False) -> ConsensusResult:
     """T rounds in float32/float64 (CUDA tensor in, CUDA tensors out)."""
     return _run(pred, False, False, n_failing, constrained, max_spread, centre, centre2, tie_rule, want_moments,
-                want_qr, want_essence)
+                want_qr, want_essence, want_rank)
 
 
 def consensus_fixed_host(pred, n_failing, **kw) -> ConsensusResult:
@@ -145,6 +147,20 @@ def expected_reliability(arrays: torch.Tensor) -> torch.Tensor:
         stream = torch.cuda.current_stream().cuda_stream
         _lib.check(_lib.load().svoc_expected_reliability(C.c_void_p(a.data_ptr()), a.shape[0], a.shape[1],
                                                          C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+    return out
+
+
+def rank_array(values: torch.Tensor) -> torch.Tensor:
+    """[T, n] float64 CUDA tensor -> [T, n] int32 ranks, largest value = rank 0 (ipynb beta :342-352)."""
+    if not values.is_cuda or values.dtype != torch.float64 or values.dim() != 2:
+        raise TypeError("expected a [T, n] float64 CUDA tensor")
+    v = values.contiguous()
+    out = torch.empty(v.shape, dtype=torch.int32, device=v.device)
+    if v.shape[0]:
+        with torch.cuda.device(v.device):
+            stream = torch.cuda.current_stream().cuda_stream
+            _lib.check(_lib.load().svoc_rank_array(C.c_void_p(v.data_ptr()), v.shape[0], v.shape[1],
+                                                   C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
     return out
 
 

@@ -100,11 +100,8 @@ class RunningStats:
     def allreduce(self, group=None):
         """SUM the local accumulators over all ranks (NCCL over NVLink on GPUs); returns (counts, sums)
         of the whole job and leaves the local accumulators untouched."""
-        import torch.distributed as dist
-        c, s = self.counts.clone(), self.sums.clone()
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-            dist.all_reduce(c, op=dist.ReduceOp.SUM, group=group)
-            dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
+        from .distributed import allreduce_stats
+        c, s = allreduce_stats(self.counts, self.sums, group)
         self._reduced = (c, s)
         return c, s
 

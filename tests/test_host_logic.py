@@ -1,0 +1,125 @@
+"""CPU: host-side logic that needs no GPU — wire codec, the contract mirror's activation gate and vote
+state machine, trial sharding and the world_size-2 all-reduce of the accumulators (gloo)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+
+def test_felt_codec_round_trips():
+    from svoc import client
+    P = client.UPPER_BOUND_FELT252
+    assert client.felt_to_i128(P - 1) == -1 and client.i128_to_felt(-1) == P - 1          # tests/test_math.cairo:95-96
+    assert client.float_to_fwsad(0.492954) == 492954 and client.float_to_fwsad(-2.5) == P - 2500000
+    assert client.fwsad_to_float(client.float_to_fwsad(-2.5)) == -2.5
+    assert client.float_to_fwsad(0.9999999) == 999999                                      # int() truncates toward zero
+    assert client.from_hex(client.to_hex(255)) == 255
+    for v in (0, 1, -1, 10**12, -(10**12), 2**126):
+        assert client.felt_to_i128(client.i128_to_felt(v)) == v
+
+
+def test_contract_mirror_gate_and_vote_without_gpu():
+    from svoc.contract import ContractPanic, OracleConsensusNDS
+    admins, oracles = ["Akashi", "Ozu", "Higuchi"], [f"oracle_{i:02d}" for i in range(7)]
+    c = OracleConsensusNDS(admins, True, 2, 2, True, 0, 2, oracles)
+    for i in range(6):                                  # no consensus (and no GPU call) until all have committed
+        c.set_caller(oracles[i])
+        c.update_prediction([400000 + i, 300000])
+        assert not c.consensus_active() and c.get_consensus_value() == [0, 0]
+    assert c.n_active_oracles == 6
+    c.set_caller(oracles[0])
+    c.update_prediction([1, 2])                          # re-commit does not count twice
+    assert c.n_active_oracles == 6
+    with pytest.raises(ContractPanic):
+        c.update_prediction([-1 % 2**251, 5])            # negative felt -> interval error
+    c.set_caller("stranger")
+    with pytest.raises(ContractPanic):
+        c.update_prediction([1, 2])
+    with pytest.raises(ContractPanic):
+        c.update_proposition((1, "x"))                   # not an admin
+    with pytest.raises(ContractPanic):
+        c.get_oracle_value_list()
+    c.set_caller(admins[2])
+    with pytest.raises(ContractPanic):
+        c.update_proposition((7, "x"))                   # wrong old oracle index
+    with pytest.raises(ContractPanic):
+        c.update_proposition((1, oracles[3]))            # already in the team
+    c.update_proposition((1, "new_1"))
+    assert c.get_a_specific_proposition(2) == (1, "new_1") and c.vote_matrix[2][2]
+    c.update_proposition((2, "new_2"))                   # changing the proposition resets its votes
+    c.set_caller(admins[0])
+    c.vote_for_a_proposition(2, True)
+    assert c.get_oracle_list()[2] == "new_2" and c.get_replacement_propositions() == [None] * 3
+    assert not any(any(r) for r in c.vote_matrix)
+    c.vote_for_a_proposition(1, True)                    # 1 vote < majority: nothing happens
+    c.set_caller(admins[1])
+    with pytest.raises(ContractPanic):
+        c.vote_for_a_proposition(1, True)                # majority reached on an empty proposition: unwrap panics
+    d = OracleConsensusNDS(admins, False, 2, 2, True, 0, 2, oracles)
+    d.set_caller(admins[0])
+    with pytest.raises(ContractPanic):
+        d.update_proposition(None)                       # replacement disabled
+
+
+def test_shard_ranges_partition_the_trials():
+    from svoc.distributed import shard_range
+    for T in (0, 1, 7, 1000, 10**9 + 7):
+        for G in (1, 2, 3, 8):
+            r = [shard_range(T, k, G) for k in range(G)]
+            assert r[0][0] == 0 and r[-1][1] == T
+            assert all(r[k][1] == r[k + 1][0] for k in range(G - 1))
+            assert max(b - a for a, b in r) - min(b - a for a, b in r) <= 1
+    with pytest.raises(ValueError):
+        shard_range(10, 2, 2)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, T, out):
+    import torch.distributed as dist
+    from oracle import cref
+    from svoc.distributed import allreduce_stats, shard_range
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(42)
+        x = (rng.beta(10, 15, (T, 7, 2)) * 1e6).astype(np.int64)        # same data on every rank, sharded by range
+        lo, hi = shard_range(T, rank, world)
+        o = cref.fixed_batch(x[lo:hi], 2, True, 0, False)
+        counts = torch.zeros(528 + 14, dtype=torch.int64)
+        sums = torch.zeros(4 + 7, dtype=torch.float64)
+        ok = o["status"] == 0
+        counts[0], counts[1] = hi - lo, int(ok.sum())
+        counts[528:535] = torch.from_numpy((~o["reliable"][ok]).sum(axis=0))
+        counts[535:542] = torch.from_numpy(o["qr"][ok].sum(axis=0))
+        sums[0] = float(o["rel1"][ok].sum()) * 1e-6
+        c, s = allreduce_stats(counts, sums)
+        if rank == 0:
+            torch.save({"counts": c, "sums": s}, out)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_allreduce_equals_single_rank(tmp_path):
+    """Two gloo ranks each reduce their own trial range; the all-reduced accumulators equal the
+    single-process result exactly (integer counters) / to rounding (float sums)."""
+    import torch.multiprocessing as mp
+    from oracle import cref
+    T, port, out = 1001, _free_port(), str(tmp_path / "r0.pt")
+    mp.spawn(_worker, args=(2, port, T, out), nprocs=2, join=True)
+    got = torch.load(out)
+    rng = np.random.default_rng(42)
+    x = (rng.beta(10, 15, (T, 7, 2)) * 1e6).astype(np.int64)
+    o = cref.fixed_batch(x, 2, True, 0, False)
+    ok = o["status"] == 0
+    assert int(got["counts"][0]) == T and int(got["counts"][1]) == int(ok.sum())
+    assert got["counts"][528:535].tolist() == (~o["reliable"][ok]).sum(axis=0).tolist()
+    assert got["counts"][535:542].tolist() == o["qr"][ok].sum(axis=0).tolist()
+    assert abs(float(got["sums"][0]) - float(o["rel1"][ok].sum()) * 1e-6) < 1e-6

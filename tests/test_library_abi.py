@@ -29,7 +29,7 @@ def test_header_symbols_are_exported_and_bound():
 def test_struct_layout_matches_header():
     from svoc import _lib
     assert C.sizeof(_lib.SvocConfig) == 56
-    assert C.sizeof(_lib.SvocOutputs) == 9 * 8
+    assert C.sizeof(_lib.SvocOutputs) == 10 * 8
     assert _lib.SvocConfig.max_spread_wsad.offset == 16 and _lib.SvocConfig.centre.offset == 32
 
 
