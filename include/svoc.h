@@ -177,6 +177,21 @@ int svoc_generate(const svoc_gen_config *cfg, int64_t n_rounds, void *pred, uint
 int svoc_accumulate_stats(const svoc_config *cfg, int64_t n_rounds, const svoc_outputs *out, int64_t *counts,
                           double *sums, void *stream);
 
+/* Fused Monte-Carlo run — the reference's `benchmark` loop (ipynb beta :385-402) as one persistent kernel:
+ * every round is drawn (as svoc_generate would, same Philox stream), reduced by the consensus round and
+ * folded into the accumulators without its predictions ever reaching HBM.  `cfg` describes the consensus
+ * (dtype SVOC_I32, SVOC_F32 or SVOC_F64 = the element type the predictions are drawn in), `gen` the
+ * workload; both must agree on n_oracles / dimension / n_failing.  counts / sums use the
+ * svoc_accumulate_stats layout with two extra slots each:
+ *   counts[528 + 2N]     rounds whose reliable set equals the honest set (identification success)
+ *   counts[528 + 2N + 1] rounds that entered the distance statistics (status 0)
+ *   sums[4 + N]          sum over those rounds of ||consensus - centre of the honest rows||
+ *   sums[4 + N + 1]      sum of its square
+ * so that 100 * (1 - 2 * sums[4+N] / counts[528+2N+1]) is the benchmark's "true consensus reliability". */
+#define SVOC_MC_EXTRA 2
+int svoc_montecarlo(const svoc_config *cfg, const svoc_gen_config *gen, int64_t n_rounds, int64_t *counts,
+                    double *sums, void *stream);
+
 const char *svoc_last_error(void);
 int svoc_version(void);
 /* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */

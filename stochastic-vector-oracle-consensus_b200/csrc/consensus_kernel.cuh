@@ -259,6 +259,151 @@ __device__ inline F reliability_float(F avg_qr, const Params &p) {
     return (F)1 - (ms > s ? s : ms) / ms;
 }
 
+// ------------------------------------------------------------------------------ one block of rounds
+// Phases 1-4 for the `nr` rounds staged at `tile` (row-major [nr][N][D]).  Outputs of round r0 + r go
+// to index (r0 - ob + r) of the output arrays, so a caller may point them at a per-block scratch.
+template <class Tr, int NPAD>
+__device__ __forceinline__ void consensus_block(const Params &p, const typename Tr::in_t *tile, i64 r0, int nr, i64 ob,
+                                                typename Tr::val_t *c1, typename Tr::acc_t *qr_s, int *stw_s,
+                                                uint8_t *keep_s) {
+    using in_t = typename Tr::in_t;
+    using val_t = typename Tr::val_t;
+    using acc_t = typename Tr::acc_t;
+    const int N = p.N, D = p.D, R = p.R;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const size_t round_elems = (size_t)N * D;
+
+    // ---- phase 1: first-pass centre of every (round, dimension) column
+    for (int c = tid; c < nr * D; c += nt) {
+        const int r = c / D, d = c - r * D;
+        const in_t *col = tile + (size_t)r * round_elems + d;
+        val_t sk, ku;
+        int stw = STW_OK;
+        val_t e1;
+        if constexpr (NPAD > 0)
+            e1 = column_centre_net<Tr, NPAD>(col, D, N, nullptr, N, p.centre, false, sk, ku, stw);
+        else
+            e1 = column_centre_generic<Tr>(col, D, N, nullptr, N, p.centre, false, sk, ku, stw);
+        c1[c] = e1;
+        if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)(r0 - ob) * D + c] = e1;
+    }
+    __syncthreads();
+
+    // ---- phase 2: per-oracle quadratic risk against the first-pass centre (math.cairo:225-238)
+    for (int w = tid; w < nr * N; w += nt) {
+        const int r = w / N, i = w - r * N;
+        const in_t *row = tile + (size_t)r * round_elems + (size_t)i * D;
+        const val_t *cc = c1 + (size_t)r * D;
+        acc_t q = 0;
+        bool bad = false;
+        int d = i % D;  // rotated start: conflict-free shared-memory reads across rows
+        for (int k = 0; k < D; ++k) {
+            const in_t x = row[d];
+            if constexpr (Tr::fixed) {
+                if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);          // math.cairo:298-310
+                else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+            }
+            q += Tr::dev(x, cc[d]);
+            d = (d + 1 == D) ? 0 : d + 1;
+        }
+        qr_s[w] = q;
+        if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)(r0 - ob) * N + w] = q;
+        if (bad) atomicMin(&stw_s[r], p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
+    }
+    __syncthreads();
+
+    // ---- phase 3a: reliable flags — rank under (value asc, index desc | asc)  (sort.cairo:96-102,
+    //      contract.cairo:345-363)
+    for (int w = tid; w < nr * N; w += nt) {
+        const int r = w / N, i = w - r * N;
+        const acc_t *q = qr_s + (size_t)r * N;
+        const acc_t mine = q[i];
+        int rank = 0;
+        if (p.tie == SVOC_TIE_HIGH_INDEX_KEPT) {
+            for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j > i)) ? 1 : 0;
+        } else {
+            for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j < i)) ? 1 : 0;
+        }
+        keep_s[w] = rank < R ? 1 : 0;
+        if (p.rank) p.rank[(size_t)(r0 - ob) * N + w] = rank;
+    }
+    __syncthreads();
+
+    // ---- phase 3b: reliabilities (one thread per round) and the packed reliable mask
+    for (int r = tid; r < nr; r += nt) {
+        const acc_t *q = qr_s + (size_t)r * N;
+        const uint8_t *kp = keep_s + (size_t)r * N;
+        acc_t s1 = 0, s2 = 0;
+        for (int i = 0; i < N; ++i) {
+            s1 += q[i];
+            if (kp[i]) s2 += q[i];
+        }
+        int stw = STW_OK;
+        if (N < 2) stw = min(stw, STW_FIRST_SHAPE);
+        const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+        if constexpr (Tr::fixed) {
+            const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
+            if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
+            i64 rel2 = 0;
+            if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+            else {
+                rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
+                if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+            }
+            reinterpret_cast<i64 *>(p.rel1)[r0 - ob + r] = rel1;
+            reinterpret_cast<i64 *>(p.rel2)[r0 - ob + r] = rel2;
+        } else {
+            const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
+            if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
+            val_t rel2 = 0;
+            if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+            else {
+                rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
+                if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
+            }
+            reinterpret_cast<val_t *>(p.rel1)[r0 - ob + r] = rel1;
+            reinterpret_cast<val_t *>(p.rel2)[r0 - ob + r] = rel2;
+        }
+        if (stw != STW_OK) atomicMin(&stw_s[r], stw);
+    }
+    if (p.reliable) {
+        for (int w = tid; w < nr * p.words; w += nt) {
+            const int r = w / p.words, k = w - r * p.words;
+            const uint8_t *kp = keep_s + (size_t)r * N;
+            uint32_t bits = 0;
+            for (int b = 0; b < 32 && k * 32 + b < N; ++b) bits |= (uint32_t)(kp[k * 32 + b] != 0) << b;
+            p.reliable[(size_t)(r0 - ob) * p.words + w] = bits;
+        }
+    }
+
+    // ---- phase 4: second-pass centre over the reliable rows (+ moments)
+    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+    for (int c = tid; c < nr * D; c += nt) {
+        const int r = c / D, d = c - r * D;
+        const in_t *col = tile + (size_t)r * round_elems + d;
+        const uint8_t *kp = keep_s + (size_t)r * N;
+        val_t sk = 0, ku = 0, cons = 0;
+        int stw = STW_OK;
+        if (!shape2) {
+            if constexpr (NPAD > 0)
+                cons = column_centre_net<Tr, NPAD>(col, D, N, kp, R, p.centre2, p.want_moments != 0, sk, ku, stw);
+            else
+                cons = column_centre_generic<Tr>(col, D, N, kp, R, p.centre2, p.want_moments != 0, sk, ku, stw);
+        }
+        reinterpret_cast<val_t *>(p.consensus)[(size_t)(r0 - ob) * D + c] = cons;
+        if (p.want_moments) {
+            if (p.skew) reinterpret_cast<val_t *>(p.skew)[(size_t)(r0 - ob) * D + c] = sk;
+            if (p.kurt) reinterpret_cast<val_t *>(p.kurt)[(size_t)(r0 - ob) * D + c] = ku;
+        }
+        if (stw != STW_OK) atomicMin(&stw_s[r], stw);
+    }
+    __syncthreads();
+    for (int r = tid; r < nr; r += nt) {
+        const int w = stw_s[r];
+        p.status[r0 - ob + r] = (w == STW_OK) ? SVOC_ST_OK : (w & 0xff);
+    }
+}
+
 // ------------------------------------------------------------------------------ the kernel
 template <class Tr, int NPAD>
 __global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) consensus_kernel(const Params p) {
@@ -309,137 +454,8 @@ __global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) consensus_kernel(const 
     }
     __syncthreads();
 
-    // ---- phase 1: first-pass centre of every (round, dimension) column
-    for (int c = tid; c < nr * D; c += nt) {
-        const int r = c / D, d = c - r * D;
-        const in_t *col = tile + (size_t)r * round_elems + d;
-        val_t sk, ku;
-        int stw = STW_OK;
-        val_t e1;
-        if constexpr (NPAD > 0)
-            e1 = column_centre_net<Tr, NPAD>(col, D, N, nullptr, N, p.centre, false, sk, ku, stw);
-        else
-            e1 = column_centre_generic<Tr>(col, D, N, nullptr, N, p.centre, false, sk, ku, stw);
-        c1[c] = e1;
-        if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r0 * D + c] = e1;
-    }
-    __syncthreads();
-
-    // ---- phase 2: per-oracle quadratic risk against the first-pass centre (math.cairo:225-238)
-    for (int w = tid; w < nr * N; w += nt) {
-        const int r = w / N, i = w - r * N;
-        const in_t *row = tile + (size_t)r * round_elems + (size_t)i * D;
-        const val_t *cc = c1 + (size_t)r * D;
-        acc_t q = 0;
-        bool bad = false;
-        int d = i % D;  // rotated start: conflict-free shared-memory reads across rows
-        for (int k = 0; k < D; ++k) {
-            const in_t x = row[d];
-            if constexpr (Tr::fixed) {
-                if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);          // math.cairo:298-310
-                else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
-            }
-            q += Tr::dev(x, cc[d]);
-            d = (d + 1 == D) ? 0 : d + 1;
-        }
-        qr_s[w] = q;
-        if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r0 * N + w] = q;
-        if (bad) atomicMin(&stw_s[r], p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
-    }
-    __syncthreads();
-
-    // ---- phase 3a: reliable flags — rank under (value asc, index desc | asc)  (sort.cairo:96-102,
-    //      contract.cairo:345-363)
-    for (int w = tid; w < nr * N; w += nt) {
-        const int r = w / N, i = w - r * N;
-        const acc_t *q = qr_s + (size_t)r * N;
-        const acc_t mine = q[i];
-        int rank = 0;
-        if (p.tie == SVOC_TIE_HIGH_INDEX_KEPT) {
-            for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j > i)) ? 1 : 0;
-        } else {
-            for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j < i)) ? 1 : 0;
-        }
-        keep_s[w] = rank < R ? 1 : 0;
-        if (p.rank) p.rank[(size_t)r0 * N + w] = rank;
-    }
-    __syncthreads();
-
-    // ---- phase 3b: reliabilities (one thread per round) and the packed reliable mask
-    for (int r = tid; r < nr; r += nt) {
-        const acc_t *q = qr_s + (size_t)r * N;
-        const uint8_t *kp = keep_s + (size_t)r * N;
-        acc_t s1 = 0, s2 = 0;
-        for (int i = 0; i < N; ++i) {
-            s1 += q[i];
-            if (kp[i]) s2 += q[i];
-        }
-        int stw = STW_OK;
-        if (N < 2) stw = min(stw, STW_FIRST_SHAPE);
-        const bool shape2 = p.constrained ? (R < 2) : (R < 1);
-        if constexpr (Tr::fixed) {
-            const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
-            if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
-            i64 rel2 = 0;
-            if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-            else {
-                rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
-                if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
-            }
-            reinterpret_cast<i64 *>(p.rel1)[r0 + r] = rel1;
-            reinterpret_cast<i64 *>(p.rel2)[r0 + r] = rel2;
-        } else {
-            const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
-            if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
-            val_t rel2 = 0;
-            if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-            else {
-                rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
-                if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
-            }
-            reinterpret_cast<val_t *>(p.rel1)[r0 + r] = rel1;
-            reinterpret_cast<val_t *>(p.rel2)[r0 + r] = rel2;
-        }
-        if (stw != STW_OK) atomicMin(&stw_s[r], stw);
-    }
-    if (p.reliable) {
-        for (int w = tid; w < nr * p.words; w += nt) {
-            const int r = w / p.words, k = w - r * p.words;
-            const uint8_t *kp = keep_s + (size_t)r * N;
-            uint32_t bits = 0;
-            for (int b = 0; b < 32 && k * 32 + b < N; ++b) bits |= (uint32_t)(kp[k * 32 + b] != 0) << b;
-            p.reliable[(size_t)r0 * p.words + w] = bits;
-        }
-    }
-
-    // ---- phase 4: second-pass centre over the reliable rows (+ moments)
-    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
-    for (int c = tid; c < nr * D; c += nt) {
-        const int r = c / D, d = c - r * D;
-        const in_t *col = tile + (size_t)r * round_elems + d;
-        const uint8_t *kp = keep_s + (size_t)r * N;
-        val_t sk = 0, ku = 0, cons = 0;
-        int stw = STW_OK;
-        if (!shape2) {
-            if constexpr (NPAD > 0)
-                cons = column_centre_net<Tr, NPAD>(col, D, N, kp, R, p.centre2, p.want_moments != 0, sk, ku, stw);
-            else
-                cons = column_centre_generic<Tr>(col, D, N, kp, R, p.centre2, p.want_moments != 0, sk, ku, stw);
-        }
-        reinterpret_cast<val_t *>(p.consensus)[(size_t)r0 * D + c] = cons;
-        if (p.want_moments) {
-            if (p.skew) reinterpret_cast<val_t *>(p.skew)[(size_t)r0 * D + c] = sk;
-            if (p.kurt) reinterpret_cast<val_t *>(p.kurt)[(size_t)r0 * D + c] = ku;
-        }
-        if (stw != STW_OK) atomicMin(&stw_s[r], stw);
-    }
-    __syncthreads();
-    for (int r = tid; r < nr; r += nt) {
-        const int w = stw_s[r];
-        p.status[r0 + r] = (w == STW_OK) ? SVOC_ST_OK : (w & 0xff);
-    }
+    consensus_block<Tr, NPAD>(p, tile, r0, nr, 0, c1, qr_s, stw_s, keep_s);
 }
-
 
 // ------------------------------------------------------------------------------ launch
 struct Plan {

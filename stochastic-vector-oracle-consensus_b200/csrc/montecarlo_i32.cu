@@ -1,0 +1,8 @@
+// montecarlo_i32.cu — instantiates the fused Monte-Carlo kernels for one element type.
+#include "montecarlo.cuh"
+
+namespace svoc {
+int montecarlo_i32(const Params &p, const McParams &m, int npad, int threads, size_t smem, int grid, cudaStream_t st) {
+    return dispatch_mc<FixedTr<int32_t>>(p, m, npad, threads, smem, grid, st);
+}
+}  // namespace svoc

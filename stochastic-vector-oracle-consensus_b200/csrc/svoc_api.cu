@@ -9,6 +9,7 @@
 #include <cstdlib>
 
 #include "consensus_wide.cuh"
+#include "montecarlo.cuh"
 
 namespace svoc {
 
@@ -167,6 +168,52 @@ int consensus_device(const svoc_config *cfg, const void *pred, int64_t T, const 
     }
 }
 
+int montecarlo_device(const svoc_config *cfg, const svoc_gen_config *gen, int64_t T, int64_t *counts, double *sums,
+                      void *stream) {
+    if (!cfg || !gen || !counts || !sums) return fail("null argument");
+    if (T < 0) return fail("negative round count");
+    if (T == 0) return 0;
+    if (!(cfg->dtype == SVOC_I32 || cfg->dtype == SVOC_F32 || cfg->dtype == SVOC_F64))
+        return fail("montecarlo supports dtype I32, F32 and F64");
+    if (cfg->n_oracles < 2 || cfg->dimension < 1 || cfg->n_failing < 0 || cfg->n_failing >= cfg->n_oracles)
+        return fail("bad shape");
+    if (gen->n_oracles != cfg->n_oracles || gen->dimension != cfg->dimension || gen->n_failing != cfg->n_failing)
+        return fail("consensus and generator configurations disagree on the shape");
+    if (gen->n_params < 1 || gen->n_params > SVOC_MAX_LAW_PARAMS) return fail("n_params out of range");
+    if (cfg->centre < 0 || cfg->centre > 2 || cfg->centre2 < -1 || cfg->centre2 > 2 || cfg->tie_rule < 0 || cfg->tie_rule > 1)
+        return fail("bad centre / tie rule");
+    if ((i64)cfg->n_oracles * cfg->dimension >= 0xFFFF0000LL) return fail("n_oracles * dimension too large");
+    svoc_config c = *cfg;
+    c.want_moments = 0;
+    const size_t es = elem_size(c.dtype), vs = (c.dtype == SVOC_F32) ? 4 : 8;
+    const int npad = npad_for(c.n_oracles);
+    const int threads = npad ? 128 : 256;
+    int rb = threads / c.dimension;
+    if (rb < 1) rb = 1;
+    const size_t budget = npad ? 44 * 1024 : 200 * 1024;
+    while (rb > 1 && mc_smem_bytes(c.n_oracles, c.dimension, rb, es, vs) > budget) rb >>= 1;
+    const size_t smem = mc_smem_bytes(c.n_oracles, c.dimension, rb, es, vs);
+    if (smem > 220 * 1024) return fail("a round does not fit in shared memory for the fused Monte-Carlo kernel");
+    Plan pl{};
+    pl.npad = npad; pl.rb = rb; pl.threads = threads; pl.tile_smem = 1; pl.smem = smem;
+    svoc_outputs none{};
+    Params p = make_params(c, nullptr, T, none, pl);
+    McParams m;
+    m.gen = *gen;
+    m.gen.dtype = c.dtype;
+    m.counts = reinterpret_cast<u64 *>(counts);
+    m.sums = sums;
+    m.n_blocks = (T + rb - 1) / rb;
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(16, (200 * 1024) / std::max<size_t>(smem, 1)));
+    const int grid = (int)std::min<i64>(m.n_blocks, (i64)sm_count() * per_sm);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (c.dtype) {
+        case SVOC_I32: return montecarlo_i32(p, m, npad, threads, smem, grid, st);
+        case SVOC_F32: return montecarlo_f32(p, m, npad, threads, smem, grid, st);
+        default: return montecarlo_f64(p, m, npad, threads, smem, grid, st);
+    }
+}
+
 void set_error(const std::string &m) { g_err = m; }
 void count_launch() {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -186,6 +233,11 @@ int svoc_consensus_fixed(const svoc_config *cfg, const void *pred, int64_t n_rou
 int svoc_consensus_float(const svoc_config *cfg, const void *pred, int64_t n_rounds, const svoc_outputs *out,
                          void *stream) {
     return svoc::consensus_device(cfg, pred, n_rounds, out, stream, false);
+}
+
+int svoc_montecarlo(const svoc_config *cfg, const svoc_gen_config *gen, int64_t n_rounds, int64_t *counts,
+                    double *sums, void *stream) {
+    return svoc::montecarlo_device(cfg, gen, n_rounds, counts, sums, stream);
 }
 
 const char *svoc_last_error(void) { return svoc::g_err.c_str(); }

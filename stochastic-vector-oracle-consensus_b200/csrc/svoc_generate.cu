@@ -6,8 +6,7 @@
 // Everything is a pure function of (seed, global trial, oracle, dim).
 #include <string>
 
-#include "philox.cuh"
-#include "svoc_common.cuh"
+#include "generate_device.cuh"
 
 namespace svoc {
 int fail(const std::string &m);
@@ -20,77 +19,6 @@ struct GenParams {
     uint32_t *honest;
     int rb, words;
 };
-
-__device__ __forceinline__ float normal_from(uint32_t r0, uint32_t r1) {
-    // Box-Muller, cosine branch
-    const float u = u01(r0), v = u01(r1);
-    return sqrtf(-2.0f * __logf(u)) * __cosf(6.2831853071795864f * v);
-}
-
-// Marsaglia & Tsang (2000) gamma(alpha, 1) for alpha >= 1; alpha < 1 via gamma(alpha+1) * U^(1/alpha).
-__device__ inline float gamma_draw(float alpha, uint32_t t_lo, uint32_t t_hi, uint32_t slot, uint32_t &iter,
-                                   uint32_t k0, uint32_t k1) {
-    const bool boost = alpha < 1.0f;
-    const float al = boost ? alpha + 1.0f : alpha;
-    const float d = al - 1.0f / 3.0f, c = rsqrtf(9.0f * d);
-    float out = d;
-    for (int guard = 0; guard < 64; ++guard) {
-        const Philox4 r = philox4x32_10(t_lo, t_hi, slot, iter++, k0, k1);
-        const float x = normal_from(r.v[0], r.v[1]);
-        float v = 1.0f + c * x;
-        if (v <= 0.0f) continue;
-        v = v * v * v;
-        const float u = u01(r.v[2]);
-        const float x2 = x * x;
-        if (u < 1.0f - 0.0331f * x2 * x2 || logf(u) < 0.5f * x2 + d * (1.0f - v + logf(v))) {
-            out = d * v;
-            if (boost) out *= powf(u01(r.v[3]), 1.0f / alpha);
-            break;
-        }
-    }
-    return out;
-}
-
-__device__ __forceinline__ float beta_mode(float a, float b) { return (a - 1.0f) / (a + b - 2.0f); }  // ipynb beta :80-81
-
-template <class Out>
-__device__ __forceinline__ Out convert_out(float x);
-template <> __device__ __forceinline__ float convert_out<float>(float x) { return x; }
-template <> __device__ __forceinline__ double convert_out<double>(float x) { return (double)x; }
-template <> __device__ __forceinline__ int32_t convert_out<int32_t>(float x) { return (int32_t)(x * 1e6f); }     // to_wsad
-template <> __device__ __forceinline__ i64 convert_out<i64>(float x) { return (i64)((double)x * 1e6); }
-
-// One prediction component of the notebook generators.
-__device__ __forceinline__ float draw_component(const svoc_gen_config &c, bool is_failing, uint32_t t_lo, uint32_t t_hi,
-                                                int oracle, int d, uint32_t k0, uint32_t k1) {
-    const int pi = d % c.n_params;
-    const float a = (float)c.a[pi], b = (float)c.b[pi];
-    const uint32_t slot = (uint32_t)(oracle * c.dimension + d);
-    uint32_t iter = 0;
-    if (is_failing) {
-        if (c.failing == SVOC_FAIL_COLLUDING) {
-            if (c.law == SVOC_LAW_BETA) return fminf(fmaxf(beta_mode(a, b) + (float)c.shift, 0.0f), 1.0f);
-            return a + (float)c.shift * b;
-        }
-        const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0x80000000u, k0, k1);
-        const float u = u01(r.v[0]);
-        if (c.law == SVOC_LAW_BETA) return u;                 // np.random.uniform(0, 1)
-        return a + u * (5.0f * b - a);                        // np.random.uniform(mu, 5 sigma)
-    }
-    if (c.law == SVOC_LAW_BETA) {
-        const float ga = gamma_draw(a, t_lo, t_hi, slot, iter, k0, k1);
-        iter = 0x40000000u;
-        const float gb = gamma_draw(b, t_lo, t_hi, slot, iter, k0, k1);
-        return ga / (ga + gb);
-    }
-    const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0, k0, k1);
-    return a + b * normal_from(r.v[0], r.v[1]);
-}
-
-// failing flags of one round: the F smallest position keys (a uniformly random F-subset)
-__device__ __forceinline__ uint32_t position_key(uint32_t t_lo, uint32_t t_hi, int oracle, uint32_t k0, uint32_t k1) {
-    return philox4x32_10(t_lo, t_hi, 0xFFFF0000u + (uint32_t)oracle, 0, k0, k1).v[0];
-}
 
 template <class Out>
 __global__ void __launch_bounds__(256) generate_kernel(const GenParams p) {

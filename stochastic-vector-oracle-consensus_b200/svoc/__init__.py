@@ -5,7 +5,7 @@ from ._lib import (CENTRE_DEFAULT, CENTRE_MEAN, CENTRE_MEDIAN, CENTRE_SMOOTH_MED
 from .engine import (WSAD, ConsensusResult, consensus_fixed, consensus_fixed_host, consensus_float,  # noqa: F401
                      consensus_float_host, expected_reliability, kernel_variant, rank_array)
 
-from .workload import Generated, RunningStats, generate  # noqa: F401
+from .workload import Generated, RunningStats, generate, montecarlo  # noqa: F401
 from . import client, contract, distributed, notebook  # noqa: F401,E402
 
 __version__ = "0.1.0"

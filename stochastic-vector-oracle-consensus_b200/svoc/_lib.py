@@ -55,7 +55,7 @@ class SvocGenConfig(C.Structure):
 
 LAW_BETA, LAW_GAUSSIAN = 0, 1
 FAIL_UNIFORM, FAIL_COLLUDING = 0, 1
-STATS_COUNTS_BASE, STATS_SUMS_BASE, STATS_HIST_BINS = 528, 4, 256
+STATS_COUNTS_BASE, STATS_SUMS_BASE, STATS_HIST_BINS, MC_EXTRA = 528, 4, 256, 2
 
 # every symbol include/svoc.h declares: name -> (restype, argtypes)
 SYMBOLS = {
@@ -66,6 +66,7 @@ SYMBOLS = {
     "svoc_expected_reliability": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "svoc_rank_array": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "svoc_generate": (C.c_int, [C.POINTER(SvocGenConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "svoc_montecarlo": (C.c_int, [C.POINTER(SvocConfig), C.POINTER(SvocGenConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "svoc_accumulate_stats": (C.c_int, [C.POINTER(SvocConfig), C.c_int64, C.POINTER(SvocOutputs), C.c_void_p, C.c_void_p, C.c_void_p]),
     "svoc_last_error": (C.c_char_p, []),
     "svoc_version": (C.c_int, []),

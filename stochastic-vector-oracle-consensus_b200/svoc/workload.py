@@ -39,6 +39,20 @@ def _seq(v, n=8):
     return v
 
 
+def _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype) -> SvocGenConfig:
+    av, bv = _seq(a), _seq(b)
+    if len(av) != len(bv):
+        raise ValueError("a and b need the same length")
+    cfg = SvocGenConfig(n_oracles=int(n_oracles), dimension=int(dimension), n_failing=int(n_failing),
+                        law={"beta": _lib.LAW_BETA, "gaussian": _lib.LAW_GAUSSIAN}[law],
+                        failing={"uniform": _lib.FAIL_UNIFORM, "colluding": _lib.FAIL_COLLUDING}[failing],
+                        dtype=_DTYPES[dtype], n_params=len(av), reserved=0, shift=float(shift),
+                        seed=int(seed) & (2**64 - 1), trial_offset=int(trial_offset))
+    for k, (x, y) in enumerate(zip(av, bv)):
+        cfg.a[k], cfg.b[k] = float(x), float(y)
+    return cfg
+
+
 def generate(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="beta", failing="uniform", shift=0.15,
              seed=0, trial_offset=0, dtype=torch.float32, device=None) -> Generated:
     """Draw `n_rounds` rounds of oracle predictions on the device.
@@ -51,16 +65,7 @@ def generate(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="bet
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     if device.type != "cuda":
         raise ValueError("svoc.generate runs on a CUDA device only")
-    av, bv = _seq(a), _seq(b)
-    if len(av) != len(bv):
-        raise ValueError("a and b need the same length")
-    cfg = SvocGenConfig(n_oracles=int(n_oracles), dimension=int(dimension), n_failing=int(n_failing),
-                        law={"beta": _lib.LAW_BETA, "gaussian": _lib.LAW_GAUSSIAN}[law],
-                        failing={"uniform": _lib.FAIL_UNIFORM, "colluding": _lib.FAIL_COLLUDING}[failing],
-                        dtype=_DTYPES[dtype], n_params=len(av), reserved=0, shift=float(shift),
-                        seed=int(seed) & (2**64 - 1), trial_offset=int(trial_offset))
-    for k, (x, y) in enumerate(zip(av, bv)):
-        cfg.a[k], cfg.b[k] = float(x), float(y)
+    cfg = _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype)
     pred = torch.empty((n_rounds, n_oracles, dimension), dtype=dtype, device=device)
     words = torch.empty((n_rounds, (n_oracles + 31) // 32), dtype=torch.int32, device=device)
     if n_rounds:
@@ -71,6 +76,27 @@ def generate(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="bet
     return Generated(pred, words, n_oracles)
 
 
+def montecarlo(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="beta", failing="uniform", shift=0.15,
+               seed=0, trial_offset=0, dtype=torch.float32, constrained=True, max_spread=0, centre=_lib.CENTRE_MEDIAN,
+               centre2=_lib.CENTRE_DEFAULT, tie_rule=_lib.TIE_LOW_INDEX_KEPT, stats: "RunningStats" = None, device=None):
+    """Fused generate -> consensus -> accumulate for `n_rounds` rounds (trials trial_offset ..): the
+    reference's `benchmark` loop (ipynb beta :385-402) without materialising a single prediction.
+    Returns the RunningStats it accumulated into (a new one unless `stats` is given)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    if stats is None:
+        stats = RunningStats(n_oracles, device=device)
+    fixed = dtype in (torch.int32, torch.int64)
+    cfg = make_config(n_oracles, dimension, n_failing, _DTYPES[dtype], constrained, max_spread, centre, centre2, tie_rule)
+    gen = _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype)
+    if n_rounds:
+        with torch.cuda.device(device):
+            st = torch.cuda.current_stream().cuda_stream
+            _lib.check(_lib.load().svoc_montecarlo(C.byref(cfg), C.byref(gen), int(n_rounds), C.c_void_p(stats.counts.data_ptr()),
+                                                   C.c_void_p(stats.sums.data_ptr()), C.c_void_p(st)))
+    stats.fixed = fixed
+    return stats
+
+
 class RunningStats:
     """Accumulators over many rounds: status counts, rel1/rel2 histograms (256 bins over [0, 1]),
     per-oracle "not reliable" counts and per-oracle sum of quadratic risk."""
@@ -78,8 +104,8 @@ class RunningStats:
     def __init__(self, n_oracles: int, device=None):
         self.n = int(n_oracles)
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-        self.counts = torch.zeros(_lib.STATS_COUNTS_BASE + 2 * self.n, dtype=torch.int64, device=self.device)
-        self.sums = torch.zeros(_lib.STATS_SUMS_BASE + self.n, dtype=torch.float64, device=self.device)
+        self.counts = torch.zeros(_lib.STATS_COUNTS_BASE + 2 * self.n + _lib.MC_EXTRA, dtype=torch.int64, device=self.device)
+        self.sums = torch.zeros(_lib.STATS_SUMS_BASE + self.n + _lib.MC_EXTRA, dtype=torch.float64, device=self.device)
         self._reduced = None
 
     def update(self, res: ConsensusResult) -> None:
@@ -110,7 +136,13 @@ class RunningStats:
         c, s = c.cpu(), s.cpu()
         B, H, n = _lib.STATS_COUNTS_BASE, _lib.STATS_HIST_BINS, self.n
         ok = int(c[1])
+        mc = int(c[B + 2 * n + 1])
+        extra = {}
+        if mc:   # filled by svoc.montecarlo only
+            extra = {"identification_success_pct": 100.0 * int(c[B + 2 * n]) / mc,
+                     "true_consensus_reliability_pct": 100.0 * (1 - 2 * float(s[_lib.STATS_SUMS_BASE + n]) / mc)}
         return {
+            **extra,
             "rounds": int(c[0]), "rounds_ok": ok,
             "status_counts": {_lib.STATUS_NAMES[k]: int(c[2 + k]) for k in range(13) if int(c[2 + k])},
             "mean_rel1": float(s[0]) / ok if ok else None, "mean_rel2": float(s[1]) / ok if ok else None,
@@ -129,7 +161,7 @@ class RunningStats:
 
     def qr_sums(self, fixed: bool) -> torch.Tensor:
         B = _lib.STATS_COUNTS_BASE
-        return self.counts[B + self.n:B + 2 * self.n] if fixed else self.sums[_lib.STATS_SUMS_BASE:]
+        return self.counts[B + self.n:B + 2 * self.n] if fixed else self.sums[_lib.STATS_SUMS_BASE:_lib.STATS_SUMS_BASE + self.n]
 
     def replacement_candidates(self, min_fraction: float = 0.5) -> list:
         """Oracles flagged unreliable in at least `min_fraction` of the accepted rounds — the indices an
