@@ -370,8 +370,11 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     return centre;
 }
 
-template <class Tr, int DT, int PT, int NT>
-__global__ void __launch_bounds__(NT, 1) consensus_wide_kernel(const Params p) {
+// GT = 1: the tile is NOT staged in shared memory; the three sweeps read the round straight from global
+// memory (first sweep from HBM, the later ones from L2, the next round prefetched into L2), which
+// leaves room for two CTAs — two rounds in flight — per SM.
+template <class Tr, int DT, int PT, int NT, int GT>
+__global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
@@ -382,7 +385,7 @@ __global__ void __launch_bounds__(NT, 1) consensus_wide_kernel(const Params p) {
     auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
 
     size_t off = 0;
-    in_t *tile = reinterpret_cast<in_t *>(smem_raw);            off += al((size_t)N * D * sizeof(in_t));
+    in_t *tile_s = reinterpret_cast<in_t *>(smem_raw);          off += GT ? 0 : al((size_t)N * D * sizeof(in_t));
     val_t *c1 = reinterpret_cast<val_t *>(smem_raw + off);      off += al((size_t)D * sizeof(val_t));
     acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + off);    off += al((size_t)N * sizeof(acc_t));
     acc_t *qrp = reinterpret_cast<acc_t *>(smem_raw + off);     off += al((size_t)H * N * sizeof(acc_t));
@@ -444,17 +447,21 @@ __global__ void __launch_bounds__(NT, 1) consensus_wide_kernel(const Params p) {
 
     for (i64 r = blockIdx.x; r < p.T; r += gridDim.x) {
         const in_t *gsrc = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;
-        // ---- phase 0: stage the round
-        if (p.wBulk) {
+        // ---- phase 0: stage the round (or, GT: only pull the NEXT round towards L2)
+        const in_t *tile = GT ? gsrc : tile_s;
+        if (GT) {
+            if (tid == 0 && p.wBulk && r + gridDim.x < p.T)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
+        } else if (p.wBulk) {
             if (tid == 0) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads of the old tile before the async write
                 mbar_expect_tx(bar, round_bytes);
-                bulk_g2s(tile, gsrc, round_bytes, bar);
+                bulk_g2s(tile_s, gsrc, round_bytes, bar);
             }
             mbar_wait(bar, parity);
             parity ^= 1;
         } else {
-            for (size_t e = tid; e < round_elems; e += NT) tile[e] = gsrc[e];
+            for (size_t e = tid; e < round_elems; e += NT) tile_s[e] = gsrc[e];
         }
         if (tid == 0) *stw_s = STW_OK;
         __syncthreads();
@@ -708,10 +715,10 @@ __global__ void __launch_bounds__(NT, 1) consensus_wide_kernel(const Params p) {
 }
 
 // shared-memory footprint of the wide variant (must match the carve-up above)
-inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t es, size_t vs) {
+inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t es, size_t vs, bool global_tile = false) {
     auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
     size_t s = 0;
-    s += al((size_t)N * D * es);
+    if (!global_tile) s += al((size_t)N * D * es);
     s += al((size_t)D * vs);
     s += al((size_t)N * vs);
     s += al((size_t)H * N * vs);
@@ -731,12 +738,13 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
 
 template <class Tr>
 int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
-    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0, WIDE_THREADS>;
+    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0, WIDE_THREADS, 0>;
     // compile-time row stride and part count for the common shapes: no address arithmetic
-    if (pl.threads == 1024) kern = consensus_wide_kernel<Tr, 128, 8, 1024>;
-    else if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS>;
-    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8, WIDE_THREADS>;
-    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8, WIDE_THREADS>;
+    if (pl.tile_smem == 0) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 1>;
+    else if (pl.threads == 1024) kern = consensus_wide_kernel<Tr, 128, 8, 1024, 0>;
+    else if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0>;
+    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8, WIDE_THREADS, 0>;
+    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8, WIDE_THREADS, 0>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, pl.threads, pl.smem, st>>>(p);

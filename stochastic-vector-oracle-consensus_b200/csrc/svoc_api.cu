@@ -67,7 +67,11 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     while ((CS / 4) % 32 != 4) CS += 16;
     int H = 1;
     while (H * 2 * N <= NT && H * 2 <= D) H *= 2;
-    const size_t smem = wide_smem_bytes(N, D, P, RP, CS, H, 4, c.dtype == SVOC_F32 ? 4 : 8);
+    // SVOC_WIDE_GLOBAL=1: read the round from global memory / L2 instead of staging it (two CTAs per SM)
+    static const bool gtile = [] { const char *e = getenv("SVOC_WIDE_GLOBAL"); return e && e[0] == '1'; }();
+    const bool use_g = gtile && D == 128 && P == 4 && NT == 512 &&
+                       (reinterpret_cast<uintptr_t>(pred) & 15) == 0;
+    const size_t smem = wide_smem_bytes(N, D, P, RP, CS, H, 4, c.dtype == SVOC_F32 ? 4 : 8, use_g);
     if (smem > 227 * 1024) return false;
     pl.variant = 1;
     pl.wP = P; pl.wRP = RP; pl.wCS = CS; pl.wH = H;
@@ -75,15 +79,14 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     pl.threads = NT;
     pl.rb = 1;
     pl.npad = 0;
-    pl.tile_smem = 1;
-    (void)pred;
+    pl.tile_smem = use_g ? 0 : 1;
     return true;
 }
 
 static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
     Plan pl{};
     if (plan_wide(c, pred, pl)) {
-        pl.grid = std::min<long long>(T, sm_count());
+        pl.grid = std::min<long long>(T, (long long)sm_count() * (pl.tile_smem ? 1 : 2));
         return pl;
     }
     pl.variant = 0;
