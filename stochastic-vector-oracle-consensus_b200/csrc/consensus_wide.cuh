@@ -83,8 +83,11 @@ __device__ __forceinline__ unsigned pack4(unsigned a, unsigned b, unsigned c, un
 // bytes of y as SIGNED values subtracts 256 for every set MSB, so with the plain byte sum known
 //     #(key >= cand) = (sum_keys + rp * (128 - cand) - signed_sum(y)) / 256
 // which costs one add and one IDP.4A per four keys.
-__device__ __forceinline__ int key_byte_sum(const uint8_t *keys, int rp) {
+template <int RPT>
+__device__ __forceinline__ int key_byte_sum(const uint8_t *keys, int rp_rt) {
+    const int rp = RPT ? RPT : rp_rt;
     unsigned acc = 0;
+#pragma unroll
     for (int g = 0; g < rp; g += 16) {
         const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
         acc = __dp4a(a.x, 0x01010101u, acc);
@@ -95,9 +98,12 @@ __device__ __forceinline__ int key_byte_sum(const uint8_t *keys, int rp) {
     return (int)acc;
 }
 
-__device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp, unsigned cand, int sum_keys) {
+template <int RPT>
+__device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp_rt, unsigned cand, int sum_keys) {
+    const int rp = RPT ? RPT : rp_rt;
     const unsigned cb = (128u - cand) * 0x01010101u;
     int acc0 = 0, acc1 = 0;
+#pragma unroll
     for (int g = 0; g < rp; g += 32) {
         const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
         const uint4 b = *reinterpret_cast<const uint4 *>(keys + g + 16);
@@ -140,14 +146,16 @@ __device__ __forceinline__ unsigned wide_key(typename Tr::in_t x, typename Tr::i
     return x < lo ? 0u : (x > hi ? 126u : k);
 }
 
-template <class Tr, bool FIRST, int DT>
+template <class Tr, bool FIRST, int DT, int RPT>
 __device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename Tr::in_t *tile, const uint8_t *keep,
                                                 typename Tr::in_t lo, typename Tr::in_t hi,
                                                 const typename WideKey<Tr>::Scale &sc) {
     const int WD = DT ? DT : w.D;
-    const int row_lo = w.part * w.RP;
+    const int WRP = RPT ? RPT : w.RP;
+    const int row_lo = w.part * WRP;
     const typename Tr::in_t *ptr = tile + row_lo * WD + w.c;
-    for (int g = 0; g < w.RP; g += 16) {
+#pragma unroll 2
+    for (int g = 0; g < WRP; g += 16) {
         unsigned f[16];
         if (!keep && row_lo + g + 16 <= w.N) {   // whole group valid: no per-row checks
 #pragma unroll
@@ -169,7 +177,7 @@ __device__ __forceinline__ void wide_build_keys(const WideCtx &w, const typename
 
 // Centre of the flagged rows of every column (all rows when keep == nullptr).  Must be called by
 // all threads of the CTA (it synchronises); the result is valid in the part-0 thread of a column.
-template <class Tr, int DT, int PT>
+template <class Tr, int DT, int PT, int RPT>
 __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, const typename Tr::in_t *tile,
                                                           const uint8_t *keep, int n_valid, int kind, bool col_const,
                                                           bool col_fallback, typename Tr::in_t const_value, int &buf,
@@ -179,6 +187,7 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     using Key = WideKey<Tr>;
     const int WD = DT ? DT : w.D;
     const int WP = PT ? PT : w.P;
+    const int WRP = RPT ? RPT : w.RP;
     refined = false;
     val_t centre = 0;
     if (kind == SVOC_CENTRE_MEAN) {
@@ -195,11 +204,13 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
     centre_ranks(kind, n_valid, klo, khi);
     in_t *list = reinterpret_cast<in_t *>(w.list);
     in_t *thr = reinterpret_cast<in_t *>(w.thr), *rlo = reinterpret_cast<in_t *>(w.rlo), *rhi = reinterpret_cast<in_t *>(w.rhi);
-    const int slots = WP * w.RP;
-    const int row_lo = w.part * w.RP, row_hi = min(w.N, row_lo + w.RP);
+    const int slots = WP * WRP;
+    const int row_lo = w.part * WRP, row_hi = min(w.N, row_lo + WRP);
     const int pstride = WP * WD;                        // one buffer of partial counts
-    int *my_partial = w.partial + w.part * WD + w.c;
-    const int *col_partial = w.partial + w.c;
+    int *my_partial = w.partial + w.part * WD + w.c + buf * pstride;     // this pass's slot ...
+    int *my_partial_alt = w.partial + w.part * WD + w.c + (buf ^ 1) * pstride;   // ... and the next pass's
+    const int *col_partial = w.partial + w.c + buf * pstride;
+    const int *col_partial_alt = w.partial + w.c + (buf ^ 1) * pstride;
     int *best1 = w.best + w.c, *best2 = w.best + WD + w.c, *best3 = w.best + 2 * WD + w.c;
     const in_t *lc = list + w.c;
     bool done = !w.has_unit || col_const;
@@ -211,21 +222,23 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
         // ---- bisection over the 7 key bits for rank klo
         unsigned prefix = 0;
         int L = 0, LE = n_valid;
-        const int sum_keys = active ? key_byte_sum(w.mykeys, w.RP) : 0;
+        const int sum_keys = active ? key_byte_sum<RPT>(w.mykeys, WRP) : 0;
 #pragma unroll
         for (int bit = 6; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
-            if (active) my_partial[buf * pstride] = (int)count_ge(w.mykeys, w.RP, cand, sum_keys);
+            if (active) *my_partial = (int)count_ge<RPT>(w.mykeys, WRP, cand, sum_keys);
             unit_sync(w.bar_id, w.bar_count);
             if (active) {
                 int tot = 0;
 #pragma unroll
-                for (int q = 0; q < WP; ++q) tot += col_partial[buf * pstride + q * WD];
+                for (int q = 0; q < WP; ++q) tot += col_partial[q * WD];
                 const int lt = slots - tot;  // sentinels (127) are never below a pivot
                 if (lt <= klo) { prefix = cand; L = lt; }
                 else LE = lt;    // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
             }
             buf ^= 1;
+            { int *t = my_partial; my_partial = my_partial_alt; my_partial_alt = t; }
+            { const int *t = col_partial; col_partial = col_partial_alt; col_partial_alt = t; }
         }
         // ---- collect the rows whose key lies in the window: the bucket of rank klo alone when rank khi
         //      is inside it too, else that bucket and the next two
@@ -234,7 +247,8 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
             const unsigned up = prefix + span > 127u ? 127u : prefix + span;
             const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
             uint32_t kmin = 0xffffffffu, kmax = 0u;
-            for (int g = 0; g < w.RP; g += 32) {
+#pragma unroll
+            for (int g = 0; g < WRP; g += 32) {
                 const uint4 a = *reinterpret_cast<const uint4 *>(w.mykeys + g);
                 const uint4 b = *reinterpret_cast<const uint4 *>(w.mykeys + g + 16);
                 unsigned acc = (a.x + c1b) & ~(a.x + c2b) & 0x80808080u;
@@ -358,7 +372,7 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
             const in_t a = rlo[w.c], b = rhi[w.c];
             typename Key::Scale sc;
             Key::make(a, b, sc);
-            wide_build_keys<Tr, false, DT>(w, tile, keep, a, b, sc);
+            wide_build_keys<Tr, false, DT, RPT>(w, tile, keep, a, b, sc);
             refined = true;
         }
         const int more = unit_sync_or(w.bar_id, w.bar_count, f == 2);
@@ -373,14 +387,14 @@ __device__ __forceinline__ typename Tr::val_t wide_centre(const WideCtx &w, cons
 // GT = 1: the tile is NOT staged in shared memory; the three sweeps read the round straight from global
 // memory (first sweep from HBM, the later ones from L2, the next round prefetched into L2), which
 // leaves room for two CTAs — two rounds in flight — per SM.
-template <class Tr, int DT, int PT, int NT, int GT>
+template <class Tr, int DT, int PT, int NT, int GT, int RPT>
 __global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
     using Key = WideKey<Tr>;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int N = p.N, D = DT ? DT : p.D, R = p.R, P = PT ? PT : p.wP, RP = p.wRP, CS = p.wCS, H = p.wH;
+    const int N = p.N, D = DT ? DT : p.D, R = p.R, P = PT ? PT : p.wP, RP = RPT ? RPT : p.wRP, CS = p.wCS, H = p.wH;
     const int tid = threadIdx.x;
     auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
 
@@ -496,7 +510,7 @@ __global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Pa
             typename Key::Scale sc;
             col_fb = !col_const && !Key::make(lo, hi, sc);
             if (!col_const && !col_fb) {
-                wide_build_keys<Tr, true, DT>(w, tile, nullptr, lo, hi, sc);
+                wide_build_keys<Tr, true, DT, RPT>(w, tile, nullptr, lo, hi, sc);
             } else {
                 for (int g = 0; g < RP; g += 16) *reinterpret_cast<uint4 *>(w.mykeys + g) = make_uint4(0, 0, 0, 0);
             }
@@ -504,7 +518,7 @@ __global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Pa
         }
         // ---- phase 1c: first-pass centre
         bool refined1 = false, refined2 = false;
-        const val_t e1 = wide_centre<Tr, DT, PT>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
+        const val_t e1 = wide_centre<Tr, DT, PT, RPT>(w, tile, nullptr, N, p.centre, col_const, col_fb, cval, buf, refined1);
         if (w.has_unit && w.part == 0) {
             c1[w.c] = e1;
             if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * D + w.c] = e1;
@@ -671,7 +685,7 @@ __global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Pa
         // refined keys behind, so the unit is re-keyed rather than patched)
         if (w.has_unit && !col_const && !col_fb) {
             if (refined1) {
-                wide_build_keys<Tr, true, DT>(w, tile, keep_s, lo0, hi0, sc0);
+                wide_build_keys<Tr, true, DT, RPT>(w, tile, keep_s, lo0, hi0, sc0);
             } else {
                 for (int g = 0; g < RP; g += 32) {   // dropped rows of this unit -> sentinel key
                     const int base = row_lo + g;
@@ -687,7 +701,7 @@ __global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Pa
         }
         // ---- phase 4: second-pass centre over the reliable rows (+ moments)
         val_t cons = 0;
-        if (!shape2) cons = wide_centre<Tr, DT, PT>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
+        if (!shape2) cons = wide_centre<Tr, DT, PT, RPT>(w, tile, keep_s, R, p.centre2, col_const, col_fb, cval, buf, refined2);
         if (w.has_unit && w.part == 0) {
             reinterpret_cast<val_t *>(p.consensus)[(size_t)r * D + w.c] = cons;
             if (p.want_moments) {
@@ -738,13 +752,16 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
 
 template <class Tr>
 int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
-    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0, WIDE_THREADS, 0>;
-    // compile-time row stride and part count for the common shapes: no address arithmetic
-    if (pl.tile_smem == 0) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 1>;
-    else if (pl.threads == 1024) kern = consensus_wide_kernel<Tr, 128, 8, 1024, 0>;
-    else if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0>;
-    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8, WIDE_THREADS, 0>;
-    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8, WIDE_THREADS, 0>;
+    void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0, WIDE_THREADS, 0, 0>;
+    // compile-time row stride, part count and rows per part for the common shapes: no address arithmetic,
+    // fully unrolled key loops
+    if (pl.tile_smem == 0 && p.wRP == 64) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 1, 64>;
+    else if (pl.tile_smem == 0) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 1, 0>;
+    else if (pl.threads == 1024) kern = consensus_wide_kernel<Tr, 128, 8, 1024, 0, 0>;
+    else if (p.D == 128 && p.wP == 4 && p.wRP == 64) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0, 64>;
+    else if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0, 0>;
+    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8, WIDE_THREADS, 0, 0>;
+    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8, WIDE_THREADS, 0, 0>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, pl.threads, pl.smem, st>>>(p);
