@@ -67,8 +67,9 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     while ((CS / 4) % 32 != 4) CS += 16;
     int H = 1;
     while (H * 2 * N <= NT && H * 2 <= D) H *= 2;
-    // SVOC_WIDE_GLOBAL=1: read the round from global memory / L2 instead of staging it (two CTAs per SM)
-    static const bool gtile = [] { const char *e = getenv("SVOC_WIDE_GLOBAL"); return e && e[0] == '1'; }();
+    // Default for the 128-dimension shape: read the round from global memory / L2 instead of staging it,
+    // which leaves room for two CTAs (two rounds in flight) per SM.  SVOC_WIDE_GLOBAL=0 forces staging.
+    static const bool gtile = [] { const char *e = getenv("SVOC_WIDE_GLOBAL"); return !(e && e[0] == '0'); }();
     const bool use_g = gtile && D == 128 && P == 4 && NT == 512 &&
                        (reinterpret_cast<uintptr_t>(pred) & 15) == 0;
     const size_t smem = wide_smem_bytes(N, D, P, RP, CS, H, 4, c.dtype == SVOC_F32 ? 4 : 8, use_g);

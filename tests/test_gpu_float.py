@@ -126,3 +126,26 @@ def test_full_size_properties_c4():
     torch.testing.assert_close(r2.qr, r.qr, rtol=1e-4, atol=1e-7)
     kept = x[:, F:, :]
     torch.testing.assert_close(r.consensus, 0.5 * (kept.sort(dim=1).values[:, (N - F) // 2 - 1] + kept.sort(dim=1).values[:, (N - F) // 2]))
+
+
+@pytest.mark.parametrize("N,D,F", [(256, 128, 51), (100, 3, 20), (65, 7, 13)])
+def test_rank_output_and_threshold_search_agree(N, D, F):
+    """The wide variant finds the reliable set either by ranking every row (when ranks are requested) or
+    by a histogram threshold search: both must give the same flags, and the ranks must order qr."""
+    import svoc
+    g = svoc.generate(64, N, D, F, a=10, b=15, failing="colluding", shift=0.02, seed=3)   # colluders tie exactly
+    for tie in (svoc.TIE_HIGH_INDEX_KEPT, svoc.TIE_LOW_INDEX_KEPT):
+        a = svoc.consensus_float(g.pred, F, tie_rule=tie, want_rank=True)
+        b = svoc.consensus_float(g.pred, F, tie_rule=tie, want_rank=False)
+        assert torch.equal(a.reliable_words, b.reliable_words) and torch.equal(a.consensus, b.consensus)
+        rank = a.rank.long()
+        assert torch.equal(rank.sort(dim=1).values, torch.arange(N, device=rank.device).expand(64, N))
+        assert torch.equal(a.reliable, rank < N - F)
+        q_sorted = torch.gather(a.qr, 1, rank.argsort(dim=1))
+        assert torch.all(q_sorted[:, 1:] >= q_sorted[:, :-1])
+        # among equal qr the tie rule orders by index
+        idx = rank.argsort(dim=1)
+        same = q_sorted[:, 1:] == q_sorted[:, :-1]
+        step = idx[:, 1:] - idx[:, :-1]
+        assert torch.all(step[same] < 0) if tie == svoc.TIE_HIGH_INDEX_KEPT else torch.all(step[same] > 0)
+        assert same.any()
