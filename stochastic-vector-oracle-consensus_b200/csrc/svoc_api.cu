@@ -8,7 +8,7 @@
 #include <algorithm>
 #include <cstdlib>
 
-#include "consensus_wide.cuh"
+#include "consensus_col.cuh"
 #include "montecarlo.cuh"
 
 namespace svoc {
@@ -84,9 +84,42 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     return true;
 }
 
+// column variant: one thread per column, a group of ceil32(D) threads per round, several rounds per CTA;
+// needs 16-byte aligned rounds (vector loads, L2 prefetch).  SVOC_VARIANT=wide|generic overrides.
+static bool plan_col(const svoc_config &c, const void *pred, Plan &pl) {
+    const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
+    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
+    if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
+    static const std::string force = [] { const char *e = getenv("SVOC_VARIANT"); return std::string(e ? e : ""); }();
+    if (force == "wide" || force == "generic") return false;
+    const size_t round_bytes = (size_t)N * D * 4;
+    if ((reinterpret_cast<uintptr_t>(pred) & 15) != 0 || (round_bytes & 15) != 0) return false;
+    const int G = (D + 31) & ~31;
+    const int NP = (N + 31) & ~31;
+    int CS = NP;
+    while ((CS / 4) % 32 != 4) CS += 16;
+    const size_t per = col_group_smem(N, D, G, CS, 4, c.dtype == SVOC_F32 ? 4 : 8);
+    int groups = std::min<int>(COL_THREADS / G, 16);
+    while (groups > 1 && per * groups > 227 * 1024) --groups;
+    if (per * groups > 227 * 1024) return false;
+    pl.variant = 2;
+    pl.wP = G; pl.wRP = (int)per; pl.wCS = CS; pl.wH = groups;
+    pl.smem = per * groups;
+    pl.threads = COL_THREADS;
+    pl.rb = 1;
+    pl.npad = 0;
+    pl.tile_smem = 0;
+    return true;
+}
+
 static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
     Plan pl{};
-    if (plan_wide(c, pred, pl)) {
+    if (plan_col(c, pred, pl)) {
+        pl.grid = std::min<long long>((T + pl.wH - 1) / pl.wH, sm_count());
+        return pl;
+    }
+    static const std::string force = [] { const char *e = getenv("SVOC_VARIANT"); return std::string(e ? e : ""); }();
+    if (force != "generic" && plan_wide(c, pred, pl)) {
         pl.grid = std::min<long long>(T, (long long)sm_count() * (pl.tile_smem ? 1 : 2));
         return pl;
     }
@@ -255,7 +288,8 @@ const char *svoc_kernel_variant(const svoc_config *cfg) {
     if (!cfg) return "invalid";
     const int np = svoc::npad_for(cfg->n_oracles);
     svoc::Plan pl{};
-    if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
+    if (svoc::plan_col(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "column");
+    else if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
     else if (np) snprintf(buf, sizeof buf, "small%d", np);
     else snprintf(buf, sizeof buf, "generic");
     return buf;
