@@ -71,6 +71,7 @@ __device__ __forceinline__ typename Tr::val_t col_centre(const ColCtx &w, const 
     using Key = WideKey<Tr>;
     const int WD = DT ? DT : w.D;
     const int NP = NPT ? NPT : w.NP;
+    const int LD = DT ? ((DT + 31) & ~31) : w.LD;
     refined = false;
     if (kind == SVOC_CENTRE_MEAN) {
         val_t s = 0;
@@ -107,8 +108,13 @@ __device__ __forceinline__ typename Tr::val_t col_centre(const ColCtx &w, const 
         const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
         uint32_t kmin = 0xffffffffu, kmax = 0u;
         int m = 0;
-#pragma unroll 2
-        for (int g = 0; g < NP; g += 32) {
+        // First the row indices of the window (no loads), then their values with four loads in flight.
+        // Row index k lives in the upper half of this column's list (two per 32-bit slot, slots 16..31),
+        // value k in slot k: a value only ever overwrites row indices that were already consumed.
+        auto row_slot = [&](int k) -> unsigned short & {
+            return reinterpret_cast<unsigned short *>(&lc[(COL_CAP / 2 + (k >> 1)) * LD])[k & 1];
+        };
+        auto window_flags = [&](int g) {
             const uint4 a = *reinterpret_cast<const uint4 *>(w.keys + g);
             const uint4 b = *reinterpret_cast<const uint4 *>(w.keys + g + 16);
             unsigned acc = (a.x + c1b) & ~(a.x + c2b) & 0x80808080u;
@@ -119,16 +125,42 @@ __device__ __forceinline__ typename Tr::val_t col_centre(const ColCtx &w, const 
             acc |= ((b.y + c1b) & ~(b.y + c2b) & 0x80808080u) >> 5;
             acc |= ((b.z + c1b) & ~(b.z + c2b) & 0x80808080u) >> 6;
             acc |= ((b.w + c1b) & ~(b.w + c2b) & 0x80808080u) >> 7;
+            return acc;
+        };
+#pragma unroll 2
+        for (int g = 0; g < NP; g += 32) {
+            unsigned acc = window_flags(g);
             while (acc) {
                 const int pos = __ffs(acc) - 1;
                 acc &= acc - 1;
-                const int row = g + 4 * (7 - (pos & 7)) + (pos >> 3);
-                const in_t x = col[row * WD];
-                const uint32_t kx = okey(x);
-                kmin = kx < kmin ? kx : kmin;
-                kmax = kx > kmax ? kx : kmax;
-                if (m < COL_CAP) lc[m * w.LD] = x;
+                if (m < COL_CAP) row_slot(m) = (unsigned short)(g + 4 * (7 - (pos & 7)) + (pos >> 3));
                 ++m;
+            }
+        }
+        if (m <= COL_CAP) {
+            int k = 0;
+            for (; k + 4 <= m; k += 4) {
+                in_t xs[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) xs[u] = col[(int)row_slot(k + u) * WD];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) lc[(k + u) * LD] = xs[u];
+            }
+            for (; k < m; ++k) {
+                const in_t x = col[(int)row_slot(k) * WD];
+                lc[k * LD] = x;
+            }
+        } else {
+            // crowded window (rare): only its value range is needed for the re-keying
+            for (int g = 0; g < NP; g += 32) {
+                unsigned acc = window_flags(g);
+                while (acc) {
+                    const int pos = __ffs(acc) - 1;
+                    acc &= acc - 1;
+                    const uint32_t kx = okey(col[(g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD]);
+                    kmin = kx < kmin ? kx : kmin;
+                    kmax = kx > kmax ? kx : kmax;
+                }
             }
         }
         const int j1 = klo - L, j2 = khi - L;
@@ -138,9 +170,10 @@ __device__ __forceinline__ typename Tr::val_t col_centre(const ColCtx &w, const 
             // lt(v) = #{u < v}; the value of rank j is the candidate with the largest lt <= j
             int b1 = -1, b2 = -1, b3 = -1;
             for (int a = 0; a < m; ++a) {
-                const in_t v = lc[a * w.LD];
+                const in_t v = lc[a * LD];
                 int rk = 0;
-                for (int b = 0; b < m; ++b) rk += lc[b * w.LD] < v ? 1 : 0;
+#pragma unroll 4
+                for (int b = 0; b < m; ++b) rk += lc[b * LD] < v ? 1 : 0;
                 if (rk <= j1 && rk > b1) { b1 = rk; v_lo = v; }
                 if (rk <= j2 && rk > b2) { b2 = rk; v_hi = v; }
                 if (rk > b3) { b3 = rk; thr = v; }
@@ -229,7 +262,7 @@ __global__ void __launch_bounds__(COL_THREADS, 1) consensus_col_kernel(const Par
         const in_t *gsrc = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;
         if (t == 0) {
             *stw_s = STW_OK;
-            if (p.wBulk && r + stride < p.T)    // pull this group's next round towards L2
+            if (p.wBulk && p.tile_smem && r + stride < p.T)    // pull this group's next round towards L2 (only when it fits)
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc + (size_t)stride * round_elems), "r"(round_bytes) : "memory");
         }
         const in_t *col = gsrc + t;
@@ -238,14 +271,29 @@ __global__ void __launch_bounds__(COL_THREADS, 1) consensus_col_kernel(const Par
         in_t lo = 0, hi = 0;
         typename Key::Scale sc{};
         if (has_col) {
+            // Key scale from the first 64 rows only: values outside it clamp to the end buckets, which keeps
+            // the keys monotone (a crowded end bucket is re-keyed like any other).  A degenerate sample
+            // falls back to the exact sweep, which also decides whether the column is constant.
             lo = std::numeric_limits<in_t>::max();
             hi = std::numeric_limits<in_t>::lowest();
-            const in_t *ptr = col;
+            const int ns = N < 64 ? N : 64;
+            {
+                const in_t *ptr = col;
 #pragma unroll 16
-            for (int row = 0; row < N; ++row, ptr += D) {
-                const in_t x = *ptr;
-                lo = vmin(lo, x);
-                hi = vmax(hi, x);
+                for (int row = 0; row < ns; ++row, ptr += D) {
+                    const in_t x = *ptr;
+                    lo = vmin(lo, x);
+                    hi = vmax(hi, x);
+                }
+            }
+            if (!(hi > lo)) {
+                const in_t *ptr = col + (size_t)ns * D;
+#pragma unroll 16
+                for (int row = ns; row < N; ++row, ptr += D) {
+                    const in_t x = *ptr;
+                    lo = vmin(lo, x);
+                    hi = vmax(hi, x);
+                }
             }
             col_const = !(hi > lo);
             col_fb = !col_const && !Key::make(lo, hi, sc);
@@ -276,8 +324,20 @@ __global__ void __launch_bounds__(COL_THREADS, 1) consensus_col_kernel(const Par
                     in_t x[8];
                     memcpy(&x[0], &xa, 16);
                     memcpy(&x[4], &xb, 16);
+                    val_t cc[8];
+                    if constexpr (sizeof(val_t) == 4) {
+                        const int4 ca = *reinterpret_cast<const int4 *>(c1 + d), cb = *reinterpret_cast<const int4 *>(c1 + d + 4);
+                        memcpy(&cc[0], &ca, 16);
+                        memcpy(&cc[4], &cb, 16);
+                    } else {
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) one(x[k], c1[d + k]);
+                        for (int k = 0; k < 8; k += 2) {
+                            const int4 cv = *reinterpret_cast<const int4 *>(c1 + d + k);
+                            memcpy(&cc[k], &cv, 16);
+                        }
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) one(x[k], cc[k]);
                 }
             } else {
                 for (int d = 0; d < D; ++d) one(row[d], c1[d]);

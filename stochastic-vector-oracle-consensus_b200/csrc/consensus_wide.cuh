@@ -46,7 +46,8 @@ struct WideKey<FixedTr<int32_t>> {
         return true;
     }
     __device__ static __forceinline__ float t(int32_t x, const Scale &s) {
-        return __saturatef((float)((uint32_t)x - (uint32_t)s.lo) * s.inv);
+        // values below the scale's origin clamp to 0 (the unsigned difference would wrap)
+        return x < s.lo ? 0.0f : __saturatef((float)((uint32_t)x - (uint32_t)s.lo) * s.inv);
     }
 };
 

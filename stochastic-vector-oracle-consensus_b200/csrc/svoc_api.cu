@@ -108,7 +108,9 @@ static bool plan_col(const svoc_config &c, const void *pred, Plan &pl) {
     pl.threads = COL_THREADS;
     pl.rb = 1;
     pl.npad = 0;
-    pl.tile_smem = 0;
+    // tile_smem doubles as "prefetch the next round into L2": only when current + next rounds of every group
+    // on every SM stay well inside the 126 MB L2
+    pl.tile_smem = ((size_t)sm_count() * groups * 2 * round_bytes <= (size_t)64 << 20) ? 1 : 0;
     return true;
 }
 
