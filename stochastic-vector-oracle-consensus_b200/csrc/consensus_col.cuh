@@ -380,9 +380,14 @@ __global__ void __launch_bounds__(COL_THREADS, 1) consensus_col_kernel(const Par
                     return c;
                 };
                 rank = count(0, i0, high) + count(i1, N, !high);
-                for (int j = i0; j < i1; ++j) {
-                    const acc_t q = qr_s[j];
-                    rank += (q < mine || (q == mine && (high ? j > i : j < i))) ? 1 : 0;
+                {   // the warp's own 32 rows: ties decided by index
+                    int lt = 0, eq = 0;
+                    if (high) {
+                        for (int j = i0; j < i1; ++j) { const acc_t q = qr_s[j]; lt += q < mine ? 1 : 0; eq += (q == mine) & (j > i) ? 1 : 0; }
+                    } else {
+                        for (int j = i0; j < i1; ++j) { const acc_t q = qr_s[j]; lt += q < mine ? 1 : 0; eq += (q == mine) & (j < i) ? 1 : 0; }
+                    }
+                    rank += lt + eq;
                 }
                 if (ok) {
                     keep_s[i] = rank < R ? 1 : 0;
@@ -440,6 +445,10 @@ __global__ void __launch_bounds__(COL_THREADS, 1) consensus_col_kernel(const Par
                 reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
             }
             if (stw != STW_OK) atomicMin(stw_s, stw);
+            if (!p.want_moments) {   // every contribution to the status is in: publish it now
+                const int sw = *stw_s;
+                p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+            }
         }
         // ---- phase 4: second-pass centre over the reliable rows
         if (has_col) {
@@ -478,10 +487,14 @@ __global__ void __launch_bounds__(COL_THREADS, 1) consensus_col_kernel(const Par
                 if (stw != STW_OK) atomicMin(stw_s, stw);
             }
         }
-        group_sync(bar_id, G);   // the group's shared state may be reused
-        if (t == 0) {
-            const int sw = *stw_s;
-            p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+        // Without moments nothing after this point touches the group's shared state before the next round's
+        // first barrier, so fast threads may run ahead into the next round's (thread-local) first phase.
+        if (p.want_moments) {
+            group_sync(bar_id, G);
+            if (t == 0) {
+                const int sw = *stw_s;
+                p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+            }
         }
     }
 }

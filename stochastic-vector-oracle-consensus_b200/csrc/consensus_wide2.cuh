@@ -1,0 +1,591 @@
+// consensus_wide2.cuh — the `wide2` variant of the fused consensus round: 64 < N <= 512 oracles, 32-bit
+// elements (fp32 / int32), rounds aligned to 16 bytes.  This is the kernel config 4 (N=256, D=128, fp32)
+// runs.  It keeps the selection method of `wide` (monotone 7-bit keys, SWAR bisection, exact ranking of a
+// small window) and changes the work decomposition after profiling it:
+//   * the P row-parts of a column sit in the SAME warp (lane = part * (32/P) + column-in-warp), so partial
+//     counts, candidate offsets and rank results are combined with a few shuffles: the bisection has no
+//     shared-memory traffic, no atomics and no barriers;
+//   * the round is not staged in shared memory.  Its sweeps read global memory (a warp request covers
+//     P rows x 32 contiguous bytes = whole sectors): the first touch comes from HBM, the later ones from
+//     L2, and the CTA's next round is prefetched into L2 (cp.async.bulk.prefetch.L2).  Without the
+//     128 KB tile two CTAs — two rounds — share an SM and fill each other's stalls;
+//   * the key scale comes from a 64-row sample of the column (values outside it clamp to the end
+//     buckets, which keeps keys monotone), saving one sweep.
+// A CTA-wide barrier is needed only where rows meet columns (4 per round).
+// Reference semantics: see consensus_kernel.cuh (contract.cairo:442-503 etc.).
+#pragma once
+#include <type_traits>
+
+#include "consensus_wide.cuh"
+
+namespace svoc {
+
+constexpr int W2_THREADS = 512;
+constexpr int W2_CAP = 32;
+
+struct W2Ctx {
+    int N, D, RP;          // rows, dimensions, rows per part (multiple of 32)
+    int c, part;           // this thread's column and row part
+    unsigned cmask;        // the lanes that share this thread's column
+    int sh1, sh2, sh3;     // xor distances that walk over those lanes (0 = unused)
+    uint8_t *mykeys;       // keysT + c*CS + part*RP
+};
+
+template <class T>
+__device__ __forceinline__ T col_sum(const W2Ctx &w, T v) {
+    if (w.sh1) v += __shfl_xor_sync(w.cmask, v, w.sh1);
+    if (w.sh2) v += __shfl_xor_sync(w.cmask, v, w.sh2);
+    if (w.sh3) v += __shfl_xor_sync(w.cmask, v, w.sh3);
+    return v;
+}
+template <class T, class Op>
+__device__ __forceinline__ T col_reduce(const W2Ctx &w, T v, Op op) {
+    if (w.sh1) v = op(v, __shfl_xor_sync(w.cmask, v, w.sh1));
+    if (w.sh2) v = op(v, __shfl_xor_sync(w.cmask, v, w.sh2));
+    if (w.sh3) v = op(v, __shfl_xor_sync(w.cmask, v, w.sh3));
+    return v;
+}
+
+template <class Tr, bool FIRST, int DT, int RPT>
+__device__ __forceinline__ void w2_build_keys(const W2Ctx &w, const typename Tr::in_t *tile, const uint8_t *keep,
+                                              typename Tr::in_t lo, typename Tr::in_t hi,
+                                              const typename WideKey<Tr>::Scale &sc) {
+    const int WD = DT ? DT : w.D;
+    const int WRP = RPT ? RPT : w.RP;
+    const int row_lo = w.part * WRP;
+    const typename Tr::in_t *ptr = tile + row_lo * WD + w.c;
+#pragma unroll 2
+    for (int g = 0; g < WRP; g += 16) {
+        unsigned f[16];
+        if (!keep && row_lo + g + 16 <= w.N) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) f[k] = wide_key<Tr, FIRST>(ptr[k * WD], lo, hi, sc);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int row = row_lo + g + k;
+                f[k] = 127u;
+                if (row < w.N && (!keep || keep[row])) f[k] = wide_key<Tr, FIRST>(ptr[k * WD], lo, hi, sc);
+            }
+        }
+        *reinterpret_cast<uint4 *>(w.mykeys + g) =
+            make_uint4(pack4(f[0], f[1], f[2], f[3]), pack4(f[4], f[5], f[6], f[7]), pack4(f[8], f[9], f[10], f[11]),
+                       pack4(f[12], f[13], f[14], f[15]));
+        ptr += 16 * WD;
+    }
+}
+
+// Centre of the flagged rows of this thread's column (all rows when keep == nullptr).  Executed by the P
+// lanes of the column together (shuffles under w.cmask); every one of them returns the result.
+template <class Tr, int DT, int PT, int RPT>
+__device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const typename Tr::in_t *tile,
+                                                        const uint8_t *keep, int n_valid, int kind, bool col_const,
+                                                        bool col_fallback, typename Tr::in_t const_value,
+                                                        typename Tr::in_t *list, int P_rt, bool &refined) {
+    using in_t = typename Tr::in_t;
+    using val_t = typename Tr::val_t;
+    using Key = WideKey<Tr>;
+    const int WD = DT ? DT : w.D;
+    const int WP = PT ? PT : P_rt;
+    const int WRP = RPT ? RPT : w.RP;
+    refined = false;
+    const int row_lo = w.part * WRP, row_hi = min(w.N, row_lo + WRP);
+    if (kind == SVOC_CENTRE_MEAN) {
+        val_t s = 0;
+        for (int i = row_lo; i < row_hi; ++i)
+            if (!keep || keep[i]) s += (val_t)tile[i * WD + w.c];
+        return Tr::mean(col_sum(w, s), n_valid);     // integer sums are exact; float sums differ only in order
+    }
+    if (col_const) return Tr::half_sum((val_t)const_value, (val_t)const_value);
+    if (col_fallback) {
+        val_t sk, ku;
+        int stw = STW_OK;
+        return column_centre_generic<Tr>(tile + w.c, WD, w.N, keep, n_valid, kind, false, sk, ku, stw);
+    }
+    int klo, khi;
+    centre_ranks(kind, n_valid, klo, khi);
+    const int slots = WP * WRP;
+    in_t *lc = list + w.c;                        // this column's candidate values: slot k at lc[k * WD]
+    in_t v_lo = const_value, v_hi = const_value;
+
+    for (;;) {
+        // ---- bisection over the 7 key bits for rank klo: own part, then a shuffle sum over the column's lanes
+        unsigned prefix = 0;
+        int L = 0, LE = n_valid;
+        const int sum_keys = key_byte_sum<RPT>(w.mykeys, WRP);
+#pragma unroll
+        for (int bit = 6; bit >= 0; --bit) {
+            const unsigned cand = prefix | (1u << bit);
+            const int ge = col_sum(w, (int)count_ge<RPT>(w.mykeys, WRP, cand, sum_keys));
+            const int lt = slots - ge;            // sentinels (127) are never below a pivot
+            if (lt <= klo) { prefix = cand; L = lt; }
+            else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
+        }
+        // ---- the window: the bucket of rank klo alone when rank khi is inside it, else that and the next two
+        const unsigned span = (khi < LE) ? 1u : 3u;
+        const unsigned up = prefix + span > 127u ? 127u : prefix + span;
+        const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
+        // flags of this part's rows, RP/32 words (compile-time count when RPT is given)
+        unsigned fl[(RPT ? RPT : 512) / 32];
+        int mine = 0;
+#pragma unroll
+        for (int g = 0; g < (RPT ? RPT : 512); g += 32) {
+            fl[g / 32] = 0;
+            if (g < WRP) {
+                const uint4 a = *reinterpret_cast<const uint4 *>(w.mykeys + g);
+                const uint4 b = *reinterpret_cast<const uint4 *>(w.mykeys + g + 16);
+                unsigned acc = (a.x + c1b) & ~(a.x + c2b) & 0x80808080u;
+                acc |= ((a.y + c1b) & ~(a.y + c2b) & 0x80808080u) >> 1;
+                acc |= ((a.z + c1b) & ~(a.z + c2b) & 0x80808080u) >> 2;
+                acc |= ((a.w + c1b) & ~(a.w + c2b) & 0x80808080u) >> 3;
+                acc |= ((b.x + c1b) & ~(b.x + c2b) & 0x80808080u) >> 4;
+                acc |= ((b.y + c1b) & ~(b.y + c2b) & 0x80808080u) >> 5;
+                acc |= ((b.z + c1b) & ~(b.z + c2b) & 0x80808080u) >> 6;
+                acc |= ((b.w + c1b) & ~(b.w + c2b) & 0x80808080u) >> 7;
+                fl[g / 32] = acc;
+                mine += __popc(acc);
+            }
+        }
+        // slot offset of this part = candidates of the lower parts; m = all of them
+        int off = 0, m = 0;
+        {
+            const int lane_part = w.part;
+#pragma unroll
+            for (int q = 0; q < (PT ? PT : 8); ++q) {
+                if (q < WP) {
+                    const int cq = __shfl_sync(w.cmask, mine, (threadIdx.x & 31 & ~(w.sh1 | w.sh2 | w.sh3)) | (q * (32 / WP)));
+                    m += cq;
+                    if (q < lane_part) off += cq;
+                }
+            }
+        }
+        const int j1 = klo - L, j2 = khi - L;
+        bool rescue = false;
+        in_t thr = const_value;
+        uint32_t kmin = 0xffffffffu, kmax = 0u;
+        if (m <= W2_CAP) {
+            // values of this part's window rows -> slots off.., loads issued back to back
+            int k = off;
+#pragma unroll
+            for (int g = 0; g < (RPT ? RPT : 512); g += 32) {
+                unsigned acc = fl[g / 32];
+                while (acc) {
+                    const int pos = __ffs(acc) - 1;
+                    acc &= acc - 1;
+                    lc[k * WD] = tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c];
+                    ++k;
+                }
+            }
+            __syncwarp(w.cmask);
+            // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
+            int b1 = -1, b2 = -1, b3 = -1;
+            for (int base = w.part; base < m; base += 4 * WP) {
+                const int a0 = base, a1 = base + WP, a2 = base + 2 * WP, a3 = base + 3 * WP;
+                const in_t v0 = lc[a0 * WD];
+                const in_t v1 = a1 < m ? lc[a1 * WD] : v0, v2 = a2 < m ? lc[a2 * WD] : v0, v3 = a3 < m ? lc[a3 * WD] : v0;
+                int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+#pragma unroll 2
+                for (int b = 0; b < m; ++b) {
+                    const in_t u = lc[b * WD];
+                    r0 += u < v0 ? 1 : 0;
+                    r1 += u < v1 ? 1 : 0;
+                    r2 += u < v2 ? 1 : 0;
+                    r3 += u < v3 ? 1 : 0;
+                }
+                auto note = [&](int rk, int slot) {
+                    const int code = (rk << 8) | slot;
+                    if (rk <= j1 && code > b1) b1 = code;
+                    if (rk <= j2 && code > b2) b2 = code;
+                    if (code > b3) b3 = code;
+                };
+                note(r0, a0);
+                if (a1 < m) note(r1, a1);
+                if (a2 < m) note(r2, a2);
+                if (a3 < m) note(r3, a3);
+            }
+            auto imax = [](int a, int b) { return a > b ? a : b; };
+            b1 = col_reduce(w, b1, imax);
+            b2 = col_reduce(w, b2, imax);
+            b3 = col_reduce(w, b3, imax);
+            v_lo = lc[(b1 & 0xff) * WD];
+            v_hi = lc[(b2 & 0xff) * WD];
+            thr = lc[(b3 & 0xff) * WD];
+            rescue = j2 >= m;
+            __syncwarp(w.cmask);                  // the list may be overwritten by the next selection
+        } else {
+            // crowded window (rare): its value range decides between "all one value" and a finer re-keying
+#pragma unroll
+            for (int g = 0; g < (RPT ? RPT : 512); g += 32) {
+                unsigned acc = fl[g / 32];
+                while (acc) {
+                    const int pos = __ffs(acc) - 1;
+                    acc &= acc - 1;
+                    const uint32_t kx = okey(tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c]);
+                    kmin = kx < kmin ? kx : kmin;
+                    kmax = kx > kmax ? kx : kmax;
+                }
+            }
+            kmin = col_reduce(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+            kmax = col_reduce(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
+            in_t a, b;
+            unkey(kmin, a);
+            unkey(kmax, b);
+            typename Key::Scale sc;
+            if (!(b > a)) {                       // the whole window is one value
+                v_lo = a;
+                v_hi = a;
+                thr = a;
+                rescue = j2 >= m;
+            } else if (!Key::make(a, b, sc)) {
+                val_t sk, ku;
+                int stw = STW_OK;
+                return column_centre_generic<Tr>(tile + w.c, WD, w.N, keep, n_valid, kind, false, sk, ku, stw);
+            } else {
+                w2_build_keys<Tr, false, DT, RPT>(w, tile, keep, a, b, sc);
+                refined = true;
+                continue;
+            }
+        }
+        if (rescue) {                             // rank khi lies above the window: smallest flagged value above it
+            uint32_t best = 0xffffffffu;
+            const in_t *ptr = tile + row_lo * WD + w.c;
+            for (int row = row_lo; row < row_hi; ++row, ptr += WD) {
+                if (keep && !keep[row]) continue;
+                const in_t x = *ptr;
+                if (x > thr) { const uint32_t kx = okey(x); best = kx < best ? kx : best; }
+            }
+            best = col_reduce(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+            unkey(best, v_hi);
+        }
+        break;
+    }
+    return Tr::half_sum((val_t)v_lo, (val_t)v_hi);
+}
+
+template <class Tr, int DT, int PT, int RPT>
+__global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Params p) {
+    using in_t = typename Tr::in_t;
+    using val_t = typename Tr::val_t;
+    using acc_t = typename Tr::acc_t;
+    using Key = WideKey<Tr>;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int N = p.N, D = DT ? DT : p.D, R = p.R, P = PT ? PT : p.wP, RP = RPT ? RPT : p.wRP, CS = p.wCS;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+
+    size_t off = 0;
+    uint8_t *keysT = smem_raw + off;                            off += al((size_t)D * CS);
+    in_t *list = reinterpret_cast<in_t *>(smem_raw + off);      off += al((size_t)W2_CAP * D * sizeof(in_t));
+    val_t *c1 = reinterpret_cast<val_t *>(smem_raw + off);      off += al((size_t)D * sizeof(val_t));
+    acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + off);    off += al((size_t)N * sizeof(acc_t));
+    acc_t *red_s = reinterpret_cast<acc_t *>(smem_raw + off);   off += al((size_t)2 * (W2_THREADS / 32) * sizeof(acc_t));
+    uint32_t *maskw = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)(P * RP / 32 + 1) * 4);
+    int *stw_s = reinterpret_cast<int *>(smem_raw + off);       off += 16;
+    uint8_t *keep_s = smem_raw + off;
+
+    // column units: lane = part * CW + column-in-warp, CW = 32 / P columns per warp
+    const int CW = 32 / P;
+    W2Ctx w;
+    w.N = N; w.D = D; w.RP = RP;
+    w.part = lane / CW;
+    w.c = warp * CW + (lane - w.part * CW);
+    const bool has_unit = w.c < D;
+    w.cmask = 0;
+    for (int q = 0; q < P; ++q) w.cmask |= 1u << (q * CW + (lane % CW));
+    w.sh1 = P >= 2 ? CW : 0;
+    w.sh2 = P >= 4 ? 2 * CW : 0;
+    w.sh3 = P >= 8 ? 4 * CW : 0;
+    w.mykeys = keysT + (size_t)(has_unit ? w.c : 0) * CS + (size_t)w.part * RP;
+
+    // row units for the row phases: HR lanes per row inside one warp (lane = h * (32/HR) + row-in-warp)
+    const int HR = p.wH;                       // 1, 2 or 4
+    const int RW = 32 / HR;                    // rows per warp
+    const int rh = lane / RW;
+
+    const size_t round_elems = (size_t)N * D;
+    const uint32_t round_bytes = (uint32_t)(round_elems * sizeof(in_t));
+    const int row_lo = w.part * RP;
+    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+
+    for (i64 r = blockIdx.x; r < p.T; r += gridDim.x) {
+        const in_t *tile = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;
+        if (tid == 0) {
+            *stw_s = STW_OK;
+            if (r + gridDim.x < p.T)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(tile + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
+        }
+        // ---- phase 1: first-pass centre of every column
+        bool col_const = false, col_fb = false, refined1 = false, refined2 = false;
+        in_t lo = 0, hi = 0;
+        typename Key::Scale sc{};
+        if (has_unit) {
+            // key scale from a sample: the first 64/P rows of every part (values outside clamp to the end buckets)
+            lo = std::numeric_limits<in_t>::max();
+            hi = std::numeric_limits<in_t>::lowest();
+            const int ns = min(64 / P, max(0, min(N, row_lo + RP) - row_lo));
+            const in_t *ptr = tile + row_lo * D + w.c;
+#pragma unroll 16
+            for (int k = 0; k < ns; ++k, ptr += D) {
+                const in_t x = *ptr;
+                lo = vmin(lo, x);
+                hi = vmax(hi, x);
+            }
+            lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+            hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+            if (!(hi > lo)) {                    // degenerate sample: exact sweep, which also detects a constant column
+                const in_t *q = tile + row_lo * D + w.c;
+                for (int row = row_lo; row < min(N, row_lo + RP); ++row, q += D) {
+                    const in_t x = *q;
+                    lo = vmin(lo, x);
+                    hi = vmax(hi, x);
+                }
+                lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+                hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+            }
+            col_const = !(hi > lo);
+            col_fb = !col_const && !Key::make(lo, hi, sc);
+            if (!col_const && !col_fb) w2_build_keys<Tr, true, DT, RPT>(w, tile, nullptr, lo, hi, sc);
+            const val_t e1 = w2_centre<Tr, DT, PT, RPT>(w, tile, nullptr, N, p.centre, col_const, col_fb, lo, list, P, refined1);
+            if (w.part == 0) {
+                c1[w.c] = e1;
+                if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * D + w.c] = e1;
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 2: quadratic risk of every row; the HR lanes of a row take a slice of the dimensions each
+        for (int ib = warp * RW; ib < N; ib += (W2_THREADS / 32) * RW) {     // warp-uniform trip count
+            const int i = ib + (lane - rh * RW);
+            const bool ok = i < N;
+            const int dh = (((D + HR - 1) / HR) + 7) & ~7, dlo = rh * dh, dhi = min(D, dlo + dh);
+            acc_t q = 0;
+            bool bad = false;
+            auto one = [&](in_t x, val_t c) {
+                if constexpr (Tr::fixed) {
+                    if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
+                    else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+                }
+                q += Tr::dev(x, c);
+            };
+            if (ok) {
+                const in_t *row = tile + (size_t)i * D;
+                if ((D & 7) == 0) {
+#pragma unroll 4
+                    for (int d = dlo; d < dhi; d += 8) {
+                        const int4 xa = *reinterpret_cast<const int4 *>(row + d);
+                        const int4 xb = *reinterpret_cast<const int4 *>(row + d + 4);
+                        in_t x[8];
+                        memcpy(&x[0], &xa, 16);
+                        memcpy(&x[4], &xb, 16);
+                        val_t cc[8];
+                        if constexpr (sizeof(val_t) == 4) {
+                            const int4 ca = *reinterpret_cast<const int4 *>(c1 + d), cb = *reinterpret_cast<const int4 *>(c1 + d + 4);
+                            memcpy(&cc[0], &ca, 16);
+                            memcpy(&cc[4], &cb, 16);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < 8; k += 2) {
+                                const int4 cv = *reinterpret_cast<const int4 *>(c1 + d + k);
+                                memcpy(&cc[k], &cv, 16);
+                            }
+                        }
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) one(x[k], cc[k]);
+                    }
+                } else {
+                    for (int d = dlo; d < dhi; ++d) one(row[d], c1[d]);
+                }
+            }
+            if (HR >= 2) q += __shfl_xor_sync(0xffffffffu, q, RW);
+            if (HR >= 4) q += __shfl_xor_sync(0xffffffffu, q, 2 * RW);
+            if (ok && rh == 0) {
+                qr_s[i] = q;
+                if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * N + i] = q;
+            }
+            if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
+        }
+        __syncthreads();
+
+        // ---- phase 3: rank of every row under (qr asc, index desc | asc); the HR lanes of a row split the
+        //      comparison range and add up by shuffle.  One compare per pair outside the warp's own rows.
+        {
+            const bool high = p.tie == SVOC_TIE_HIGH_INDEX_KEPT;
+            for (int ib = warp * RW; ib < N; ib += (W2_THREADS / 32) * RW) {
+                const int i = ib + (lane - rh * RW);
+                const bool ok = i < N;
+                const acc_t mine = qr_s[ok ? i : 0];
+                const int i1 = min(N, ib + RW);             // the warp's rows are [ib, i1)
+                const int jh = (((N + HR - 1) / HR) + 3) & ~3, jlo = rh * jh, jhi = min(N, jlo + jh);
+                int tie = 0;
+                // [jlo, jhi) minus the warp's own rows: one compare per pair, strict on one side of the warp's
+                // rows and non-strict on the other
+                auto count = [&](auto strict, int a, int b) {
+                    int c = 0, j = a;
+                    auto hit = [&](acc_t q) { if constexpr (decltype(strict)::value) return q < mine ? 1 : 0; else return q <= mine ? 1 : 0; };
+                    if constexpr (sizeof(acc_t) == 4) {
+                        for (; j < b && (j & 3); ++j) c += hit(qr_s[j]);
+                        for (; j + 4 <= b; j += 4) {
+                            const float4 v = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(qr_s) + j);
+                            acc_t q0, q1, q2, q3;
+                            memcpy(&q0, &v.x, 4); memcpy(&q1, &v.y, 4); memcpy(&q2, &v.z, 4); memcpy(&q3, &v.w, 4);
+                            c += (hit(q0) + hit(q1)) + (hit(q2) + hit(q3));
+                        }
+                    }
+                    for (; j < b; ++j) c += hit(qr_s[j]);
+                    return c;
+                };
+                const int a_end = min(jhi, max(jlo, ib)), b_beg = max(jlo, min(jhi, i1));
+                int rank = high ? count(std::true_type{}, jlo, a_end) + count(std::false_type{}, b_beg, jhi)
+                                : count(std::false_type{}, jlo, a_end) + count(std::true_type{}, b_beg, jhi);
+                for (int j = a_end; j < b_beg; ++j) {
+                    const acc_t q = qr_s[j];
+                    tie += (q < mine ? 1 : 0) + (((q == mine) & (high ? j > i : j < i)) ? 1 : 0);
+                }
+                rank += tie;
+                if (HR >= 2) rank += __shfl_xor_sync(0xffffffffu, rank, RW);
+                if (HR >= 4) rank += __shfl_xor_sync(0xffffffffu, rank, 2 * RW);
+                if (ok && rh == 0) {
+                    keep_s[i] = rank < R ? 1 : 0;
+                    if (p.rank) p.rank[(size_t)r * N + i] = rank;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- mask words and the two sums
+        {
+            const int nw = (P * RP) / 32;
+            for (int k = tid; k < nw; k += W2_THREADS) {
+                uint32_t bits = 0;
+                const uint32_t *kw = reinterpret_cast<const uint32_t *>(keep_s + k * 32);
+                if (k * 32 + 32 <= N) {
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const uint32_t v = kw[q];     // four flag bytes (0 / 1)
+                        bits |= ((v & 1u) | ((v >> 7) & 2u) | ((v >> 14) & 4u) | ((v >> 21) & 8u)) << (4 * q);
+                    }
+                } else {
+                    for (int b = 0; b < 32 && k * 32 + b < N; ++b) bits |= (uint32_t)(keep_s[k * 32 + b] != 0) << b;
+                }
+                maskw[k] = bits;
+                if (p.reliable && k < p.words) p.reliable[(size_t)r * p.words + k] = bits;
+            }
+            acc_t s1 = 0, s2 = 0;
+            for (int i = tid; i < N; i += W2_THREADS) {
+                const acc_t q = qr_s[i];
+                s1 += q;
+                if (keep_s[i]) s2 += q;
+            }
+            for (int o = 16; o; o >>= 1) {
+                s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            }
+            if (lane == 0) { red_s[warp] = s1; red_s[W2_THREADS / 32 + warp] = s2; }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            acc_t s1 = 0, s2 = 0;
+            for (int k = 0; k < W2_THREADS / 32; ++k) { s1 += red_s[k]; s2 += red_s[W2_THREADS / 32 + k]; }
+            int stw = STW_OK;
+            if constexpr (Tr::fixed) {
+                const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
+                if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
+                i64 rel2 = 0;
+                if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                else {
+                    rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
+                    if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+                }
+                reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
+                reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
+            } else {
+                const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
+                if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
+                val_t rel2 = 0;
+                if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                else {
+                    rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
+                    if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
+                }
+                reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
+                reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
+            }
+            if (stw != STW_OK) atomicMin(stw_s, stw);
+        }
+        // ---- phase 4: second-pass centre over the reliable rows (+ moments)
+        if (has_unit) {
+            val_t cons = 0;
+            if (!shape2) {
+                if (!col_const && !col_fb && p.centre2 != SVOC_CENTRE_MEAN) {
+                    if (refined1) {
+                        w2_build_keys<Tr, true, DT, RPT>(w, tile, keep_s, lo, hi, sc);
+                    } else {
+                        for (int g = 0; g < RP; g += 32) {   // dropped rows of this part -> sentinel key
+                            const int base = row_lo + g;
+                            unsigned drop = ~maskw[base >> 5];
+                            if (base + 32 > N) drop &= (base < N) ? ((1u << (N - base)) - 1u) : 0u;
+                            while (drop) {
+                                const int b = __ffs(drop) - 1;
+                                drop &= drop - 1;
+                                w.mykeys[g + b] = 127;
+                            }
+                        }
+                    }
+                }
+                cons = w2_centre<Tr, DT, PT, RPT>(w, tile, keep_s, R, p.centre2, col_const, col_fb, lo, list, P, refined2);
+            }
+            if (w.part == 0) {
+                reinterpret_cast<val_t *>(p.consensus)[(size_t)r * D + w.c] = cons;
+                if (p.want_moments) {
+                    val_t sk = 0, ku = 0;
+                    int stw = STW_OK;
+                    if (!shape2) {
+                        const in_t *col = tile + w.c;
+                        auto fe = [&](auto f) {
+                            for (int i = 0; i < N; ++i)
+                                if (keep_s[i]) f(col[(size_t)i * D]);
+                        };
+                        column_moments<Tr>(fe, R, sk, ku, stw);
+                    }
+                    if (p.skew) reinterpret_cast<val_t *>(p.skew)[(size_t)r * D + w.c] = sk;
+                    if (p.kurt) reinterpret_cast<val_t *>(p.kurt)[(size_t)r * D + w.c] = ku;
+                    if (stw != STW_OK) atomicMin(stw_s, stw);
+                }
+            }
+        }
+        __syncthreads();   // keep flags, mask words and the status word are final and free again
+        if (tid == 0) {
+            const int sw = *stw_s;
+            p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+        }
+    }
+}
+
+inline size_t wide2_smem_bytes(int N, int D, int P, int RP, int CS, size_t es, size_t vs) {
+    auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+    size_t s = 0;
+    s += al((size_t)D * CS);
+    s += al((size_t)W2_CAP * D * es);
+    s += al((size_t)D * vs);
+    s += al((size_t)N * vs);
+    s += al((size_t)2 * (W2_THREADS / 32) * vs);
+    s += al((size_t)(P * RP / 32 + 1) * 4);
+    s += 16;
+    s += al((size_t)N);
+    return s;
+}
+
+template <class Tr>
+int launch_wide2(const Params &p, const Plan &pl, cudaStream_t st) {
+    void (*kern)(const Params) = consensus_wide2_kernel<Tr, 0, 0, 0>;
+    if (p.D == 128 && p.wP == 4 && p.wRP == 64) kern = consensus_wide2_kernel<Tr, 128, 4, 64>;
+    else if (p.D == 128 && p.wP == 4) kern = consensus_wide2_kernel<Tr, 128, 4, 0>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+    if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    kern<<<(unsigned)pl.grid, W2_THREADS, pl.smem, st>>>(p);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
+    count_launch();
+    return 0;
+}
+
+}  // namespace svoc

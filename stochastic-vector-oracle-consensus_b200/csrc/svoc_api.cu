@@ -9,6 +9,7 @@
 #include <cstdlib>
 
 #include "consensus_col.cuh"
+#include "consensus_wide2.cuh"
 #include "montecarlo.cuh"
 
 namespace svoc {
@@ -90,8 +91,6 @@ static bool plan_col(const svoc_config &c, const void *pred, Plan &pl) {
     const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
     if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
     if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
-    static const std::string force = [] { const char *e = getenv("SVOC_VARIANT"); return std::string(e ? e : ""); }();
-    if (force == "wide" || force == "generic") return false;
     const size_t round_bytes = (size_t)N * D * 4;
     if ((reinterpret_cast<uintptr_t>(pred) & 15) != 0 || (round_bytes & 15) != 0) return false;
     const int G = (D + 31) & ~31;
@@ -114,14 +113,54 @@ static bool plan_col(const svoc_config &c, const void *pred, Plan &pl) {
     return true;
 }
 
+static const std::string &forced_variant() {
+    static const std::string force = [] { const char *e = getenv("SVOC_VARIANT"); return std::string(e ? e : ""); }();
+    return force;
+}
+
+// wide2 variant: parts of a column inside one warp, the round read from global memory / L2 (two CTAs per SM)
+static bool plan_wide2(const svoc_config &c, const void *pred, Plan &pl) {
+    const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
+    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
+    if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
+    const std::string &force = forced_variant();
+    if (!force.empty() && force != "wide2") return false;
+    const size_t round_bytes = (size_t)N * D * 4;
+    if ((reinterpret_cast<uintptr_t>(pred) & 15) != 0 || (round_bytes & 15) != 0) return false;
+    int P = 1;
+    while (P * 2 <= 8 && P * 2 * D <= W2_THREADS && P * 2 * 32 <= N) P *= 2;
+    const int RP = (((N + P - 1) / P) + 31) & ~31;
+    if (P * RP > 512) return false;
+    // every warp must hold whole columns: D * P threads in warps of 32 / P columns
+    if ((D * P + 31) / 32 > W2_THREADS / 32) return false;
+    int CS = P * RP;
+    while ((CS / 4) % 32 != 4) CS += 16;
+    int HR = 1;
+    while (HR * 2 <= 4 && HR * 2 * N <= W2_THREADS && D / (HR * 2) >= 8) HR *= 2;
+    if ((W2_THREADS / 32) * (32 / HR) < 1) return false;
+    const size_t smem = wide2_smem_bytes(N, D, P, RP, CS, 4, c.dtype == SVOC_F32 ? 4 : 8);
+    if (smem > 110 * 1024) return false;
+    pl.variant = 3;
+    pl.wP = P; pl.wRP = RP; pl.wCS = CS; pl.wH = HR;
+    pl.smem = smem;
+    pl.threads = W2_THREADS;
+    pl.rb = 1;
+    pl.npad = 0;
+    pl.tile_smem = 0;
+    return true;
+}
+
 static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
     Plan pl{};
-    if (plan_col(c, pred, pl)) {
+    if (plan_wide2(c, pred, pl)) {
+        pl.grid = std::min<long long>(T, (long long)sm_count() * 2);
+        return pl;
+    }
+    if (forced_variant() == "column" && plan_col(c, pred, pl)) {
         pl.grid = std::min<long long>((T + pl.wH - 1) / pl.wH, sm_count());
         return pl;
     }
-    static const std::string force = [] { const char *e = getenv("SVOC_VARIANT"); return std::string(e ? e : ""); }();
-    if (force != "generic" && plan_wide(c, pred, pl)) {
+    if (forced_variant() != "generic" && plan_wide(c, pred, pl)) {
         pl.grid = std::min<long long>(T, (long long)sm_count() * (pl.tile_smem ? 1 : 2));
         return pl;
     }
@@ -290,7 +329,8 @@ const char *svoc_kernel_variant(const svoc_config *cfg) {
     if (!cfg) return "invalid";
     const int np = svoc::npad_for(cfg->n_oracles);
     svoc::Plan pl{};
-    if (svoc::plan_col(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "column");
+    if (svoc::plan_wide2(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide2");
+    else if (svoc::forced_variant() == "column" && svoc::plan_col(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "column");
     else if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
     else if (np) snprintf(buf, sizeof buf, "small%d", np);
     else snprintf(buf, sizeof buf, "generic");
