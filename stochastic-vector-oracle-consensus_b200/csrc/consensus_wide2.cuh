@@ -309,11 +309,7 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
 
     for (i64 r = blockIdx.x; r < p.T; r += gridDim.x) {
         const in_t *tile = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;
-        if (tid == 0) {
-            *stw_s = STW_OK;
-            if (r + gridDim.x < p.T)
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(tile + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
-        }
+        if (tid == 0) *stw_s = STW_OK;
         // ---- phase 1: first-pass centre of every column
         bool col_const = false, col_fb = false, refined1 = false, refined2 = false;
         in_t lo = 0, hi = 0;
@@ -353,58 +349,57 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
         }
         __syncthreads();
 
-        // ---- phase 2: quadratic risk of every row; the HR lanes of a row take a slice of the dimensions each
-        for (int ib = warp * RW; ib < N; ib += (W2_THREADS / 32) * RW) {     // warp-uniform trip count
-            const int i = ib + (lane - rh * RW);
-            const bool ok = i < N;
-            const int dh = (((D + HR - 1) / HR) + 7) & ~7, dlo = rh * dh, dhi = min(D, dlo + dh);
-            acc_t q = 0;
-            bool bad = false;
-            auto one = [&](in_t x, val_t c) {
-                if constexpr (Tr::fixed) {
-                    if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
-                    else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
-                }
-                q += Tr::dev(x, c);
-            };
-            if (ok) {
+        // ---- phase 2: quadratic risk of every row.  A warp reads one whole row per request (lane <-> 4
+        //      consecutive dimensions, 512 contiguous bytes for D = 128), so the loads are fully coalesced;
+        //      the lanes' partial sums meet in a shuffle tree (fixed order: deterministic).
+        if ((D & 3) == 0) {
+            for (int i = warp; i < N; i += W2_THREADS / 32) {
                 const in_t *row = tile + (size_t)i * D;
-                if ((D & 7) == 0) {
-#pragma unroll 4
-                    for (int d = dlo; d < dhi; d += 8) {
-                        const int4 xa = *reinterpret_cast<const int4 *>(row + d);
-                        const int4 xb = *reinterpret_cast<const int4 *>(row + d + 4);
-                        in_t x[8];
-                        memcpy(&x[0], &xa, 16);
-                        memcpy(&x[4], &xb, 16);
-                        val_t cc[8];
-                        if constexpr (sizeof(val_t) == 4) {
-                            const int4 ca = *reinterpret_cast<const int4 *>(c1 + d), cb = *reinterpret_cast<const int4 *>(c1 + d + 4);
-                            memcpy(&cc[0], &ca, 16);
-                            memcpy(&cc[4], &cb, 16);
-                        } else {
+                acc_t q = 0;
+                bool bad = false;
+                for (int d = 4 * lane; d < D; d += 128) {
+                    const int4 xv = *reinterpret_cast<const int4 *>(row + d);
+                    in_t x[4];
+                    memcpy(x, &xv, 16);
 #pragma unroll
-                            for (int k = 0; k < 8; k += 2) {
-                                const int4 cv = *reinterpret_cast<const int4 *>(c1 + d + k);
-                                memcpy(&cc[k], &cv, 16);
-                            }
+                    for (int k = 0; k < 4; ++k) {
+                        if constexpr (Tr::fixed) {
+                            if (p.constrained) bad |= (x[k] < 0) | ((i64)x[k] > WSAD);
+                            else bad |= ((i64)x[k] > ENGINE_RANGE) | ((i64)x[k] < -ENGINE_RANGE);
                         }
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) one(x[k], cc[k]);
+                        q += Tr::dev(x[k], c1[d + k]);
                     }
-                } else {
-                    for (int d = dlo; d < dhi; ++d) one(row[d], c1[d]);
                 }
+                for (int o = 16; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+                if (lane == 0) {
+                    qr_s[i] = q;
+                    if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * N + i] = q;
+                }
+                if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
             }
-            if (HR >= 2) q += __shfl_xor_sync(0xffffffffu, q, RW);
-            if (HR >= 4) q += __shfl_xor_sync(0xffffffffu, q, 2 * RW);
-            if (ok && rh == 0) {
+        } else {
+            for (int i = tid; i < N; i += W2_THREADS) {
+                const in_t *row = tile + (size_t)i * D;
+                acc_t q = 0;
+                bool bad = false;
+                for (int d = 0; d < D; ++d) {
+                    const in_t x = row[d];
+                    if constexpr (Tr::fixed) {
+                        if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
+                        else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+                    }
+                    q += Tr::dev(x, c1[d]);
+                }
                 qr_s[i] = q;
                 if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * N + i] = q;
+                if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
             }
-            if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
         }
         __syncthreads();
+        // the last full sweep of this round is done: pull the next round towards L2 now, so that it is resident
+        // only while it is about to be used
+        if (tid == 0 && r + gridDim.x < p.T)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(tile + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
 
         // ---- phase 3: rank of every row under (qr asc, index desc | asc); the HR lanes of a row split the
         //      comparison range and add up by shuffle.  One compare per pair outside the warp's own rows.
@@ -421,7 +416,20 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
                 // rows and non-strict on the other
                 auto count = [&](auto strict, int a, int b) {
                     int c = 0, j = a;
-                    auto hit = [&](acc_t q) { if constexpr (decltype(strict)::value) return q < mine ? 1 : 0; else return q <= mine ? 1 : 0; };
+                    auto hit = [&](acc_t q) {
+                        if constexpr (sizeof(acc_t) == 4) {      // set.{lt,le}.s32.f32: 0 or -1 in one instruction
+                            int d;
+                            float qf, mf;
+                            memcpy(&qf, &q, 4);
+                            memcpy(&mf, &mine, 4);
+                            if constexpr (decltype(strict)::value) asm("set.lt.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(qf), "f"(mf));
+                            else asm("set.le.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(qf), "f"(mf));
+                            return -d;
+                        } else {
+                            if constexpr (decltype(strict)::value) return q < mine ? 1 : 0;
+                            else return q <= mine ? 1 : 0;
+                        }
+                    };
                     if constexpr (sizeof(acc_t) == 4) {
                         for (; j < b && (j & 3); ++j) c += hit(qr_s[j]);
                         for (; j + 4 <= b; j += 4) {
