@@ -353,27 +353,50 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
         //      consecutive dimensions, 512 contiguous bytes for D = 128), so the loads are fully coalesced;
         //      the lanes' partial sums meet in a shuffle tree (fixed order: deterministic).
         if ((D & 3) == 0) {
-            for (int i = warp; i < N; i += W2_THREADS / 32) {
-                const in_t *row = tile + (size_t)i * D;
-                acc_t q = 0;
+            // four rows per trip: their lane partials are folded with a transposing shuffle tree
+            // (2 + 1 + 3 shuffles for four row sums instead of 4 x 5)
+            for (int i0 = 4 * warp; i0 < N; i0 += 4 * (W2_THREADS / 32)) {
+                acc_t q[4] = {0, 0, 0, 0};
                 bool bad = false;
                 for (int d = 4 * lane; d < D; d += 128) {
-                    const int4 xv = *reinterpret_cast<const int4 *>(row + d);
-                    in_t x[4];
-                    memcpy(x, &xv, 16);
+                    val_t cc[4];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        if constexpr (Tr::fixed) {
-                            if (p.constrained) bad |= (x[k] < 0) | ((i64)x[k] > WSAD);
-                            else bad |= ((i64)x[k] > ENGINE_RANGE) | ((i64)x[k] < -ENGINE_RANGE);
+                    for (int k = 0; k < 4; ++k) cc[k] = c1[d + k];
+                    int4 xv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        xv[u] = (i0 + u < N) ? *reinterpret_cast<const int4 *>(tile + (size_t)(i0 + u) * D + d) : make_int4(0, 0, 0, 0);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        in_t x[4];
+                        memcpy(x, &xv[u], 16);
+                        if (i0 + u < N) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                if constexpr (Tr::fixed) {
+                                    if (p.constrained) bad |= (x[k] < 0) | ((i64)x[k] > WSAD);
+                                    else bad |= ((i64)x[k] > ENGINE_RANGE) | ((i64)x[k] < -ENGINE_RANGE);
+                                }
+                                q[u] += Tr::dev(x[k], cc[k]);
+                            }
                         }
-                        q += Tr::dev(x[k], c1[d + k]);
                     }
                 }
-                for (int o = 16; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-                if (lane == 0) {
-                    qr_s[i] = q;
-                    if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * N + i] = q;
+                // lanes with bit 4 set end up owning rows 2,3; bit 3 picks the odd row of the pair
+                const bool up16 = lane & 16, up8 = lane & 8;
+                acc_t k0 = up16 ? q[2] : q[0], s0 = up16 ? q[0] : q[2];
+                acc_t k1 = up16 ? q[3] : q[1], s1 = up16 ? q[1] : q[3];
+                k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+                k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+                acc_t kk = up8 ? k1 : k0, ss = up8 ? k0 : k1;
+                kk += __shfl_xor_sync(0xffffffffu, ss, 8);
+                kk += __shfl_xor_sync(0xffffffffu, kk, 4);
+                kk += __shfl_xor_sync(0xffffffffu, kk, 2);
+                kk += __shfl_xor_sync(0xffffffffu, kk, 1);
+                const int mine_row = i0 + (up16 ? 2 : 0) + (up8 ? 1 : 0);
+                if ((lane & 7) == 0 && mine_row < N) {
+                    qr_s[mine_row] = kk;
+                    if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * N + mine_row] = kk;
                 }
                 if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
             }
