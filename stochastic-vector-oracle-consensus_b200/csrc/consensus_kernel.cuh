@@ -314,57 +314,76 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
 
     // ---- phase 3a: reliable flags — rank under (value asc, index desc | asc)  (sort.cairo:96-102,
     //      contract.cairo:345-363)
-    for (int w = tid; w < nr * N; w += nt) {
-        const int r = w / N, i = w - r * N;
-        const acc_t *q = qr_s + (size_t)r * N;
-        const acc_t mine = q[i];
-        int rank = 0;
-        if (p.tie == SVOC_TIE_HIGH_INDEX_KEPT) {
-            for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j > i)) ? 1 : 0;
-        } else {
-            for (int j = 0; j < N; ++j) rank += (q[j] < mine || (q[j] == mine && j < i)) ? 1 : 0;
+    {
+        const bool high = p.tie == SVOC_TIE_HIGH_INDEX_KEPT;
+        // constrained fixed form: every qr is at most D * 1e6, so when that fits 32 bits the low words decide
+        bool low32 = false;
+        if constexpr (Tr::fixed) low32 = p.constrained && (u64)D * (u64)WSAD < 0xffffffffull;
+        for (int w = tid; w < nr * N; w += nt) {
+            const int r = w / N, i = w - r * N;
+            const acc_t *q = qr_s + (size_t)r * N;
+            int rank = 0;
+            if (low32) {
+                const uint32_t *q32 = reinterpret_cast<const uint32_t *>(q);
+                const uint32_t mine = q32[2 * i];
+                int eq = 0;
+                for (int j = 0; j < N; ++j) {
+                    const uint32_t v = q32[2 * j];
+                    rank += v < mine ? 1 : 0;
+                    eq += ((v == mine) & (high ? j > i : j < i)) ? 1 : 0;
+                }
+                rank += eq;
+            } else {
+                const acc_t mine = q[i];
+                int eq = 0;
+                for (int j = 0; j < N; ++j) {
+                    const acc_t v = q[j];
+                    rank += v < mine ? 1 : 0;
+                    eq += ((v == mine) & (high ? j > i : j < i)) ? 1 : 0;
+                }
+                rank += eq;
+            }
+            keep_s[w] = rank < R ? 1 : 0;
+            if (p.rank) p.rank[(size_t)(r0 - ob) * N + w] = rank;
         }
-        keep_s[w] = rank < R ? 1 : 0;
-        if (p.rank) p.rank[(size_t)(r0 - ob) * N + w] = rank;
     }
     __syncthreads();
 
-    // ---- phase 3b: reliabilities (one thread per round) and the packed reliable mask
-    for (int r = tid; r < nr; r += nt) {
-        const acc_t *q = qr_s + (size_t)r * N;
-        const uint8_t *kp = keep_s + (size_t)r * N;
-        acc_t s1 = 0, s2 = 0;
-        for (int i = 0; i < N; ++i) {
-            s1 += q[i];
-            if (kp[i]) s2 += q[i];
-        }
-        int stw = STW_OK;
-        if (N < 2) stw = min(stw, STW_FIRST_SHAPE);
-        const bool shape2 = p.constrained ? (R < 2) : (R < 1);
-        if constexpr (Tr::fixed) {
-            const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
-            if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
-            i64 rel2 = 0;
-            if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-            else {
-                rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
-                if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+    // ---- phase 3b: reliabilities and the packed reliable mask.  Two scalar tasks per round (first- and
+    //      second-pass reliability: a sum and a Newton square root each), handed to threads spread over
+    //      the warps so that no single warp carries all the square roots.
+    {
+        const int ntask = 2 * nr;
+        const int spread = max(1, nt / max(1, ntask));     // > 1 when there are fewer tasks than threads
+        for (int task = (tid % spread == 0) ? tid / spread : ntask; task < ntask; task += nt) {
+            const int r = task >> 1, second = task & 1;
+            const acc_t *q = qr_s + (size_t)r * N;
+            const uint8_t *kp = keep_s + (size_t)r * N;
+            acc_t sum = 0;
+            if (second) { for (int i = 0; i < N; ++i) if (kp[i]) sum += q[i]; }
+            else { for (int i = 0; i < N; ++i) sum += q[i]; }
+            int stw = STW_OK;
+            const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+            if (!second && N < 2) stw = min(stw, STW_FIRST_SHAPE);
+            if (second && shape2) stw = min(stw, STW_SECOND_SHAPE);
+            const int cnt = second ? R : N;
+            if constexpr (Tr::fixed) {
+                i64 rel = 0;
+                if (!(second && shape2)) {
+                    rel = reliability_fixed(sum / (u64)cnt, p, second ? STW_SQRT_REL2 : STW_SQRT_REL1, stw);
+                    if (rel < 0 || rel > WSAD) stw = min(stw, second ? STW_REL2_RANGE : STW_REL1_RANGE);
+                }
+                reinterpret_cast<i64 *>(second ? p.rel2 : p.rel1)[r0 - ob + r] = rel;
+            } else {
+                val_t rel = 0;
+                if (!(second && shape2)) {
+                    rel = reliability_float<val_t>(sum / (val_t)cnt, p);
+                    if (!(rel >= 0 && rel <= 1)) stw = min(stw, second ? STW_REL2_RANGE : STW_REL1_RANGE);
+                }
+                reinterpret_cast<val_t *>(second ? p.rel2 : p.rel1)[r0 - ob + r] = rel;
             }
-            reinterpret_cast<i64 *>(p.rel1)[r0 - ob + r] = rel1;
-            reinterpret_cast<i64 *>(p.rel2)[r0 - ob + r] = rel2;
-        } else {
-            const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
-            if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
-            val_t rel2 = 0;
-            if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-            else {
-                rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
-                if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
-            }
-            reinterpret_cast<val_t *>(p.rel1)[r0 - ob + r] = rel1;
-            reinterpret_cast<val_t *>(p.rel2)[r0 - ob + r] = rel2;
+            if (stw != STW_OK) atomicMin(&stw_s[r], stw);
         }
-        if (stw != STW_OK) atomicMin(&stw_s[r], stw);
     }
     if (p.reliable) {
         for (int w = tid; w < nr * p.words; w += nt) {

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsvoc.so")
+LIB_PATH = os.environ.get("SVOC_LIB") or os.path.join(_HERE, "libsvoc.so")   # SVOC_LIB: A/B builds while tuning
 
 I32, I64, F32, F64 = 0, 1, 2, 3
 CENTRE_SMOOTH_MEDIAN_CAIRO, CENTRE_MEDIAN, CENTRE_MEAN, CENTRE_DEFAULT = 0, 1, 2, -1
