@@ -102,20 +102,24 @@ __device__ __forceinline__ int key_byte_sum(const uint8_t *keys, int rp_rt) {
 template <int RPT>
 __device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp_rt, unsigned cand, int sum_keys) {
     const int rp = RPT ? RPT : rp_rt;
+    // the pivot constant is split in two opaque halves so that every add is a three-input IADD3 (integer
+    // ALU pipe): the IDP.4A next to it lives on the FMA pipe, which a two-input IMAD.IADD would share
     const unsigned cb = (128u - cand) * 0x01010101u;
+    unsigned ca = cb >> 1, cc = cb - (cb >> 1);
+    asm volatile("" : "+r"(ca), "+r"(cc));
     int acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
 #pragma unroll
     for (int g = 0; g < rp; g += 32) {
         const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
         const uint4 b = *reinterpret_cast<const uint4 *>(keys + g + 16);
-        acc0 = __dp4a((int)(a.x + cb), 0x01010101, acc0);
-        acc1 = __dp4a((int)(a.y + cb), 0x01010101, acc1);
-        acc2 = __dp4a((int)(a.z + cb), 0x01010101, acc2);
-        acc3 = __dp4a((int)(a.w + cb), 0x01010101, acc3);
-        acc0 = __dp4a((int)(b.x + cb), 0x01010101, acc0);
-        acc1 = __dp4a((int)(b.y + cb), 0x01010101, acc1);
-        acc2 = __dp4a((int)(b.z + cb), 0x01010101, acc2);
-        acc3 = __dp4a((int)(b.w + cb), 0x01010101, acc3);
+        acc0 = __dp4a((int)(a.x + ca + cc), 0x01010101, acc0);
+        acc1 = __dp4a((int)(a.y + ca + cc), 0x01010101, acc1);
+        acc2 = __dp4a((int)(a.z + ca + cc), 0x01010101, acc2);
+        acc3 = __dp4a((int)(a.w + ca + cc), 0x01010101, acc3);
+        acc0 = __dp4a((int)(b.x + ca + cc), 0x01010101, acc0);
+        acc1 = __dp4a((int)(b.y + ca + cc), 0x01010101, acc1);
+        acc2 = __dp4a((int)(b.z + ca + cc), 0x01010101, acc2);
+        acc3 = __dp4a((int)(b.w + ca + cc), 0x01010101, acc3);
     }
     return (unsigned)(sum_keys + rp * (int)(128u - cand) - ((acc0 + acc1) + (acc2 + acc3))) >> 8;
 }

@@ -541,6 +541,10 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
                 reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
             }
             if (stw != STW_OK) atomicMin(stw_s, stw);
+            if (!p.want_moments) {   // nothing later contributes to the status: publish it now
+                const int sw = *stw_s;
+                p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+            }
         }
         // ---- phase 4: second-pass centre over the reliable rows (+ moments)
         if (has_unit) {
@@ -583,10 +587,15 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
                 }
             }
         }
-        __syncthreads();   // keep flags, mask words and the status word are final and free again
-        if (tid == 0) {
-            const int sw = *stw_s;
-            p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+        // Without moments nothing below touches shared state that the next round writes before its own first
+        // barrier (keys and candidate lists are private to a column's lanes), so warps run ahead into the next
+        // round's column phase instead of waiting for the slowest column here.
+        if (p.want_moments) {
+            __syncthreads();
+            if (tid == 0) {
+                const int sw = *stw_s;
+                p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+            }
         }
     }
 }
