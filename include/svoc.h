@@ -71,8 +71,13 @@ typedef struct svoc_config {
     int32_t tie_rule;         /* SVOC_TIE_* */
     int32_t dtype;            /* SVOC_I32/I64 (fixed form) or SVOC_F32/F64 (float form) */
     int32_t want_moments;     /* also compute skewness / kurtosis (contract.cairo:491-500) */
-    int32_t reserved;
+    int32_t flags;            /* SVOC_FLAG_* */
 } svoc_config;
+
+/* constrained reliability of the OBSOLETE contract, 1 - 2*sqrt(avg qr) without the division by the dimension
+ * (contract/obsolete/src/contract_nd.cairo:418, :437); it is the formula behind the "0.798" comment of
+ * contract/tests/test_contract.cairo:188 */
+#define SVOC_FLAG_OBSOLETE_RELIABILITY 1
 
 /* Output block shared by the device entry points.  Element type of the value outputs:
  * int64 for the fixed form; the input type (float / double) for the float form.
@@ -137,6 +142,10 @@ int svoc_rank_array(const double *values, int64_t n_lists, int32_t n, int32_t *r
  * parity with the reference generators is distributional. */
 #define SVOC_LAW_BETA 0      /* honest ~ beta(a, b); failing ~ uniform(0, 1) */
 #define SVOC_LAW_GAUSSIAN 1  /* honest ~ normal(a = mu, b = sigma); failing ~ uniform(mu, 5 sigma) */
+#define SVOC_LAW_KUMARASWAMY 2 /* honest ~ Kumaraswamy(a, b) by inverse CDF (only its mode formula is in the reference,
+                                  ipynb beta :77-78); failing ~ uniform(0, 1) */
+#define SVOC_LAW_ARCTAN_GAUSSIAN 3 /* honest = arctan(normal(tan(pi (a - 1/2)), b)) / pi + 1/2 with a = essence in (0,1),
+                                  b = sigma (generate_oracles, gaussian_algorithm_demo.ipynb:46-64); failing ~ uniform(0, 1) */
 #define SVOC_FAIL_UNIFORM 0
 #define SVOC_FAIL_COLLUDING 1 /* every failing oracle submits clip(mode + shift) (beta) / mu + shift*sigma (gaussian) */
 #define SVOC_MAX_LAW_PARAMS 8

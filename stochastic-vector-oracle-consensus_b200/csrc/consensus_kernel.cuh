@@ -32,7 +32,7 @@ struct Params {
     int constrained;
     i64 ms_w;
     double ms_f;
-    int centre, centre2, tie, want_moments;
+    int centre, centre2, tie, want_moments, flags;
     void *essence1, *qr, *rel1;
     uint32_t *reliable;
     void *consensus, *rel2, *skew, *kurt;
@@ -244,7 +244,9 @@ __device__ __forceinline__ typename Tr::val_t column_centre_generic(const typena
 __device__ inline i64 reliability_fixed(u64 avg_qr, const Params &p, int stw_sqrt, int &stw) {
     u64 s;
     if (p.constrained) {
-        if (!wsqrt(avg_qr / (u64)p.D, s)) { stw = min(stw, stw_sqrt); return 0; }
+        // the obsolete contract skips the division by the dimension (contract/obsolete/src/contract_nd.cairo:437)
+        const u64 v = (p.flags & SVOC_FLAG_OBSOLETE_RELIABILITY) ? avg_qr : avg_qr / (u64)p.D;
+        if (!wsqrt(v, s)) { stw = min(stw, stw_sqrt); return 0; }
         return WSAD - 2 * (i64)s;
     }
     if (!wsqrt(avg_qr, s)) { stw = min(stw, stw_sqrt); return 0; }
@@ -254,7 +256,8 @@ __device__ inline i64 reliability_fixed(u64 avg_qr, const Params &p, int stw_sqr
 }
 template <class F>
 __device__ inline F reliability_float(F avg_qr, const Params &p) {
-    if (p.constrained) return (F)1 - (F)2 * sqrt(avg_qr / (F)p.D);
+    if (p.constrained)
+        return (F)1 - (F)2 * sqrt((p.flags & SVOC_FLAG_OBSOLETE_RELIABILITY) ? avg_qr : avg_qr / (F)p.D);
     const F s = sqrt(avg_qr), ms = (F)p.ms_f;
     return (F)1 - (ms > s ? s : ms) / ms;
 }

@@ -55,13 +55,26 @@ __device__ __forceinline__ float draw_component(const svoc_gen_config &c, bool i
     uint32_t iter = 0;
     if (is_failing) {
         if (c.failing == SVOC_FAIL_COLLUDING) {
-            if (c.law == SVOC_LAW_BETA) return fminf(fmaxf(beta_mode(a, b) + (float)c.shift, 0.0f), 1.0f);
-            return a + (float)c.shift * b;
+            float centre;
+            if (c.law == SVOC_LAW_BETA) centre = beta_mode(a, b);
+            else if (c.law == SVOC_LAW_KUMARASWAMY) centre = powf((a - 1.0f) / (a * b - 1.0f), 1.0f / a);   // ipynb beta :77-78
+            else if (c.law == SVOC_LAW_ARCTAN_GAUSSIAN) centre = a;
+            else return a + (float)c.shift * b;
+            return fminf(fmaxf(centre + (float)c.shift, 0.0f), 1.0f);
         }
         const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0x80000000u, k0, k1);
         const float u = u01(r.v[0]);
-        if (c.law == SVOC_LAW_BETA) return u;                 // np.random.uniform(0, 1)
+        if (c.law != SVOC_LAW_GAUSSIAN) return u;             // np.random.uniform(0, 1)
         return a + u * (5.0f * b - a);                        // np.random.uniform(mu, 5 sigma)
+    }
+    if (c.law == SVOC_LAW_KUMARASWAMY) {                      // inverse CDF: x = (1 - (1 - u)^(1/b))^(1/a)
+        const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0, k0, k1);
+        return powf(1.0f - powf(1.0f - u01(r.v[0]), 1.0f / b), 1.0f / a);
+    }
+    if (c.law == SVOC_LAW_ARCTAN_GAUSSIAN) {                  // gaussian_algorithm_demo.ipynb:46-55
+        const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0, k0, k1);
+        const float mu = tanf(3.14159265358979f * (a - 0.5f));
+        return atanf(mu + b * normal_from(r.v[0], r.v[1])) * 0.318309886183791f + 0.5f;
     }
     if (c.law == SVOC_LAW_BETA) {
         const float ga = gamma_draw(a, t_lo, t_hi, slot, iter, k0, k1);

@@ -212,6 +212,7 @@ static Params make_params(const svoc_config &c, const void *pred, int64_t T, con
     p.centre2 = c.centre2 == SVOC_CENTRE_DEFAULT ? (c.constrained ? c.centre : SVOC_CENTRE_MEAN) : c.centre2;
     p.tie = c.tie_rule;
     p.want_moments = c.want_moments ? 1 : 0;
+    p.flags = c.flags;
     p.essence1 = o.essence1;
     p.qr = o.qr;
     p.rel1 = o.rel1;

@@ -76,10 +76,11 @@ extern "C" int svoc_generate(const svoc_gen_config *cfg, int64_t n_rounds, void 
     if (cfg->n_oracles < 1 || cfg->dimension < 1 || cfg->n_oracles > 65535) return fail("bad generator shape");
     if (cfg->n_failing < 0 || cfg->n_failing > cfg->n_oracles) return fail("n_failing out of range");
     if (cfg->n_params < 1 || cfg->n_params > SVOC_MAX_LAW_PARAMS) return fail("n_params out of range");
-    if (cfg->law != SVOC_LAW_BETA && cfg->law != SVOC_LAW_GAUSSIAN) return fail("unknown law");
+    if (cfg->law < SVOC_LAW_BETA || cfg->law > SVOC_LAW_ARCTAN_GAUSSIAN) return fail("unknown law");
     if ((i64)cfg->n_oracles * cfg->dimension >= 0xFFFF0000LL) return fail("n_oracles * dimension too large");
     for (int k = 0; k < cfg->n_params; ++k)
-        if (cfg->law == SVOC_LAW_BETA && !(cfg->a[k] > 0 && cfg->b[k] > 0)) return fail("beta parameters must be > 0");
+        if ((cfg->law == SVOC_LAW_BETA || cfg->law == SVOC_LAW_KUMARASWAMY) && !(cfg->a[k] > 0 && cfg->b[k] > 0))
+            return fail("beta / Kumaraswamy parameters must be > 0");
     GenParams p;
     p.c = *cfg;
     p.T = n_rounds;

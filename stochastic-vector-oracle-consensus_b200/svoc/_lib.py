@@ -32,7 +32,7 @@ class SvocConfig(C.Structure):
         ("n_oracles", C.c_int32), ("dimension", C.c_int32), ("n_failing", C.c_int32),
         ("constrained", C.c_int32), ("max_spread_wsad", C.c_int64), ("max_spread", C.c_double),
         ("centre", C.c_int32), ("centre2", C.c_int32), ("tie_rule", C.c_int32), ("dtype", C.c_int32),
-        ("want_moments", C.c_int32), ("reserved", C.c_int32),
+        ("want_moments", C.c_int32), ("flags", C.c_int32),
     ]
 
 
@@ -53,7 +53,8 @@ class SvocGenConfig(C.Structure):
     ]
 
 
-LAW_BETA, LAW_GAUSSIAN = 0, 1
+LAW_BETA, LAW_GAUSSIAN, LAW_KUMARASWAMY, LAW_ARCTAN_GAUSSIAN = 0, 1, 2, 3
+FLAG_OBSOLETE_RELIABILITY = 1
 FAIL_UNIFORM, FAIL_COLLUDING = 0, 1
 STATS_COUNTS_BASE, STATS_SUMS_BASE, STATS_HIST_BINS, MC_EXTRA = 528, 4, 256, 2
 

@@ -49,12 +49,13 @@ class ConsensusResult:
 
 
 def make_config(n, d, n_failing, dtype, constrained=True, max_spread=0, centre=CENTRE_SMOOTH_MEDIAN_CAIRO,
-                centre2=CENTRE_DEFAULT, tie_rule=TIE_HIGH_INDEX_KEPT, want_moments=False) -> SvocConfig:
+                centre2=CENTRE_DEFAULT, tie_rule=TIE_HIGH_INDEX_KEPT, want_moments=False, obsolete_reliability=False) -> SvocConfig:
     fixed = dtype in (_lib.I32, _lib.I64)
     return SvocConfig(n_oracles=int(n), dimension=int(d), n_failing=int(n_failing), constrained=int(bool(constrained)),
                       max_spread_wsad=int(max_spread) if fixed else 0, max_spread=0.0 if fixed else float(max_spread),
                       centre=int(centre), centre2=int(centre2), tie_rule=int(tie_rule), dtype=int(dtype),
-                      want_moments=int(bool(want_moments)), reserved=0)
+                      want_moments=int(bool(want_moments)),
+                      flags=_lib.FLAG_OBSOLETE_RELIABILITY if obsolete_reliability else 0)
 
 
 def _alloc_outputs(T, N, D, val_dtype, device, want_moments, want_qr, want_essence, pin=False, want_rank=False):
@@ -76,7 +77,7 @@ def _alloc_outputs(T, N, D, val_dtype, device, want_moments, want_qr, want_essen
 
 
 def _run(pred: torch.Tensor, fixed: bool, host: bool, n_failing, constrained, max_spread, centre, centre2, tie_rule,
-         want_moments, want_qr, want_essence, want_rank=False) -> ConsensusResult:
+         want_moments, want_qr, want_essence, want_rank=False, obsolete_reliability=False) -> ConsensusResult:
     if pred.dim() != 3:
         raise ValueError("predictions must be [T, N, D]")
     if pred.dtype not in _DTYPES:
@@ -89,7 +90,8 @@ def _run(pred: torch.Tensor, fixed: bool, host: bool, n_failing, constrained, ma
     pred = pred.contiguous()
     T, N, D = pred.shape
     lib = _lib.load()
-    cfg = make_config(N, D, n_failing, dt, constrained, max_spread, centre, centre2, tie_rule, want_moments)
+    cfg = make_config(N, D, n_failing, dt, constrained, max_spread, centre, centre2, tie_rule, want_moments,
+                      obsolete_reliability)
     val_dtype = torch.int64 if fixed else pred.dtype
     res, outs = _alloc_outputs(T, N, D, val_dtype, pred.device, want_moments, want_qr, want_essence,
                                pin=host and pred.is_pinned(), want_rank=want_rank)
@@ -108,10 +110,10 @@ def _run(pred: torch.Tensor, fixed: bool, host: bool, n_failing, constrained, ma
 
 def consensus_fixed(pred, n_failing, constrained=True, max_spread=0, centre=CENTRE_SMOOTH_MEDIAN_CAIRO,
                     centre2=CENTRE_DEFAULT, tie_rule=TIE_HIGH_INDEX_KEPT, want_moments=True, want_qr=True,
-                    want_essence=True, want_rank=False) -> ConsensusResult:
+                    want_essence=True, want_rank=False, obsolete_reliability=False) -> ConsensusResult:
     """T rounds of update_{un,}constrained_consensus on wsad integers (CUDA tensor in, CUDA tensors out)."""
     return _run(pred, True, False, n_failing, constrained, max_spread, centre, centre2, tie_rule, want_moments,
-                want_qr, want_essence, want_rank)
+                want_qr, want_essence, want_rank, obsolete_reliability)
 
 
 def consensus_float(pred, n_failing, constrained=True, max_spread=0.0, centre=CENTRE_SMOOTH_MEDIAN_CAIRO,

@@ -44,7 +44,8 @@ def _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed
     if len(av) != len(bv):
         raise ValueError("a and b need the same length")
     cfg = SvocGenConfig(n_oracles=int(n_oracles), dimension=int(dimension), n_failing=int(n_failing),
-                        law={"beta": _lib.LAW_BETA, "gaussian": _lib.LAW_GAUSSIAN}[law],
+                        law={"beta": _lib.LAW_BETA, "gaussian": _lib.LAW_GAUSSIAN, "kumaraswamy": _lib.LAW_KUMARASWAMY,
+                             "arctan_gaussian": _lib.LAW_ARCTAN_GAUSSIAN}[law],
                         failing={"uniform": _lib.FAIL_UNIFORM, "colluding": _lib.FAIL_COLLUDING}[failing],
                         dtype=_DTYPES[dtype], n_params=len(av), reserved=0, shift=float(shift),
                         seed=int(seed) & (2**64 - 1), trial_offset=int(trial_offset))

@@ -136,3 +136,15 @@ def test_full_size_properties_c3():
     small = torch.where(rel[:, :, None], x.long(), torch.full_like(x, 2 * W).long()).min(dim=1).values
     assert torch.all((r.consensus >= small) & (r.consensus <= big))
     assert torch.all(r.status == 0)
+
+
+def test_obsolete_reliability_anchor(contract_vectors):
+    """The "0.798" comment of contract/tests/test_contract.cairo:188 is the OBSOLETE contract's second-pass
+    reliability (1 - 2*sqrt(avg qr), no division by the dimension, contract/obsolete/src/contract_nd.cairo:437)."""
+    import svoc
+    v = contract_vectors["vectors"][0]
+    x = torch.tensor([v["pred"]], dtype=torch.int64, device="cuda")
+    r = svoc.consensus_fixed(x, v["n_failing"], want_moments=False, obsolete_reliability=True)
+    assert int(r.rel1[0]) == v["expected"]["obsolete_rel1"] and int(r.rel2[0]) == v["expected"]["obsolete_rel2"]
+    assert int(int(r.rel2[0]) / 1000) / 1000 == v["anchors"]["obsolete_rel2_3digits"]
+    assert r.consensus[0].tolist() == v["expected"]["consensus"]       # everything else is unchanged

@@ -132,3 +132,26 @@ def test_running_stats_match_numpy():
     sf.update(rf)
     np.testing.assert_allclose(sf.qr_sums(False).cpu().numpy(), rf.qr.double().sum(dim=0).cpu().numpy(), rtol=1e-9)
     assert sf.summary()["rounds"] == 30000
+
+
+def test_kumaraswamy_and_arctan_gaussian_laws():
+    """The two remaining laws of the drafts: Kumaraswamy (only its mode formula is in the reference, ipynb beta
+    :77-78) and the arctan-normalised gaussian of gaussian_algorithm_demo.ipynb:46-64."""
+    import svoc
+    from scipy import stats
+    a, b = 3.0, 5.0
+    g = svoc.generate(20000, 10, 2, 2, a=a, b=b, law="kumaraswamy", seed=4)
+    x, h = g.pred.cpu().numpy().astype(np.float64), g.honest.cpu().numpy()
+    hv = x[h].ravel()[:40000]
+    cdf = lambda t: 1 - (1 - np.clip(t, 0, 1) ** a) ** b          # noqa: E731  Kumaraswamy CDF
+    assert stats.kstest(hv, cdf).pvalue > 1e-3
+    assert stats.kstest(x[~h].ravel()[:20000], "uniform").pvalue > 1e-3
+    c = svoc.generate(50, 10, 2, 3, a=a, b=b, law="kumaraswamy", failing="colluding", shift=0.1, seed=4)
+    mode = ((a - 1) / (a * b - 1)) ** (1 / a)
+    assert np.allclose(c.pred.cpu().numpy()[~c.honest.cpu().numpy()], mode + 0.1, atol=1e-6)
+    e, sigma = 0.9, 5.0
+    g = svoc.generate(20000, 10, 1, 2, a=e, b=sigma, law="arctan_gaussian", seed=6)
+    x, h = g.pred.cpu().numpy().astype(np.float64), g.honest.cpu().numpy()
+    z = (np.tan(np.pi * (x[h].ravel()[:40000] - 0.5)) - np.tan(np.pi * (e - 0.5))) / sigma     # denormalize, standardise
+    assert stats.kstest(z, "norm").pvalue > 1e-3
+    assert x.min() > 0 and x.max() < 1
