@@ -757,16 +757,10 @@ inline size_t wide_smem_bytes(int N, int D, int P, int RP, int CS, int H, size_t
 
 template <class Tr>
 int launch_wide(const Params &p, const Plan &pl, cudaStream_t st) {
+    // `wide` is the fallback of `wide2` (rounds that are not 16-byte aligned): the tile is staged in shared
+    // memory.  One instantiation with compile-time strides for the 128-dimension shape, one generic.
     void (*kern)(const Params) = consensus_wide_kernel<Tr, 0, 0, WIDE_THREADS, 0, 0>;
-    // compile-time row stride, part count and rows per part for the common shapes: no address arithmetic,
-    // fully unrolled key loops
-    if (pl.tile_smem == 0 && p.wRP == 64) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 1, 64>;
-    else if (pl.tile_smem == 0) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 1, 0>;
-    else if (pl.threads == 1024) kern = consensus_wide_kernel<Tr, 128, 8, 1024, 0, 0>;
-    else if (p.D == 128 && p.wP == 4 && p.wRP == 64) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0, 64>;
-    else if (p.D == 128 && p.wP == 4) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0, 0>;
-    else if (p.D == 64 && p.wP == 8) kern = consensus_wide_kernel<Tr, 64, 8, WIDE_THREADS, 0, 0>;
-    else if (p.D == 32 && p.wP == 8) kern = consensus_wide_kernel<Tr, 32, 8, WIDE_THREADS, 0, 0>;
+    if (p.D == 128 && p.wP == 4 && p.wRP == 64) kern = consensus_wide_kernel<Tr, 128, 4, WIDE_THREADS, 0, 64>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, pl.threads, pl.smem, st>>>(p);

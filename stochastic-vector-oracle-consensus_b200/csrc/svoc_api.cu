@@ -8,7 +8,6 @@
 #include <algorithm>
 #include <cstdlib>
 
-#include "consensus_col.cuh"
 #include "consensus_wide2.cuh"
 #include "montecarlo.cuh"
 
@@ -57,9 +56,7 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
     if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
     if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
-    // 1024 threads (8 warps per scheduler) for the 128-dimension shape when the environment asks for it
-    static const bool big = [] { const char *e = getenv("SVOC_WIDE_1024"); return e && e[0] == '1'; }();
-    const int NT = (big && D == 128 && N >= 256) ? 1024 : 512;
+    const int NT = 512;
     int P = 1;
     while (P * 2 <= 8 && P * 2 * D <= NT && P * 2 * 32 <= N) P *= 2;
     const int RP = (((N + P - 1) / P) + 31) & ~31;
@@ -68,11 +65,7 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     while ((CS / 4) % 32 != 4) CS += 16;
     int H = 1;
     while (H * 2 * N <= NT && H * 2 <= D) H *= 2;
-    // Default for the 128-dimension shape: read the round from global memory / L2 instead of staging it,
-    // which leaves room for two CTAs (two rounds in flight) per SM.  SVOC_WIDE_GLOBAL=0 forces staging.
-    static const bool gtile = [] { const char *e = getenv("SVOC_WIDE_GLOBAL"); return !(e && e[0] == '0'); }();
-    const bool use_g = gtile && D == 128 && P == 4 && NT == 512 &&
-                       (reinterpret_cast<uintptr_t>(pred) & 15) == 0;
+    const bool use_g = false;
     const size_t smem = wide_smem_bytes(N, D, P, RP, CS, H, 4, c.dtype == SVOC_F32 ? 4 : 8, use_g);
     if (smem > 227 * 1024) return false;
     pl.variant = 1;
@@ -82,34 +75,6 @@ static bool plan_wide(const svoc_config &c, const void *pred, Plan &pl) {
     pl.rb = 1;
     pl.npad = 0;
     pl.tile_smem = use_g ? 0 : 1;
-    return true;
-}
-
-// column variant: one thread per column, a group of ceil32(D) threads per round, several rounds per CTA;
-// needs 16-byte aligned rounds (vector loads, L2 prefetch).  SVOC_VARIANT=wide|generic overrides.
-static bool plan_col(const svoc_config &c, const void *pred, Plan &pl) {
-    const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
-    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
-    if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
-    const size_t round_bytes = (size_t)N * D * 4;
-    if ((reinterpret_cast<uintptr_t>(pred) & 15) != 0 || (round_bytes & 15) != 0) return false;
-    const int G = (D + 31) & ~31;
-    const int NP = (N + 31) & ~31;
-    int CS = NP;
-    while ((CS / 4) % 32 != 4) CS += 16;
-    const size_t per = col_group_smem(N, D, G, CS, 4, c.dtype == SVOC_F32 ? 4 : 8);
-    int groups = std::min<int>(COL_THREADS / G, 16);
-    while (groups > 1 && per * groups > 227 * 1024) --groups;
-    if (per * groups > 227 * 1024) return false;
-    pl.variant = 2;
-    pl.wP = G; pl.wRP = (int)per; pl.wCS = CS; pl.wH = groups;
-    pl.smem = per * groups;
-    pl.threads = COL_THREADS;
-    pl.rb = 1;
-    pl.npad = 0;
-    // tile_smem doubles as "prefetch the next round into L2": only when current + next rounds of every group
-    // on every SM stay well inside the 126 MB L2
-    pl.tile_smem = ((size_t)sm_count() * groups * 2 * round_bytes <= (size_t)64 << 20) ? 1 : 0;
     return true;
 }
 
@@ -154,10 +119,6 @@ static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
     Plan pl{};
     if (plan_wide2(c, pred, pl)) {
         pl.grid = std::min<long long>(T, (long long)sm_count() * 2);
-        return pl;
-    }
-    if (forced_variant() == "column" && plan_col(c, pred, pl)) {
-        pl.grid = std::min<long long>((T + pl.wH - 1) / pl.wH, sm_count());
         return pl;
     }
     if (forced_variant() != "generic" && plan_wide(c, pred, pl)) {
@@ -331,7 +292,6 @@ const char *svoc_kernel_variant(const svoc_config *cfg) {
     const int np = svoc::npad_for(cfg->n_oracles);
     svoc::Plan pl{};
     if (svoc::plan_wide2(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide2");
-    else if (svoc::forced_variant() == "column" && svoc::plan_col(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "column");
     else if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
     else if (np) snprintf(buf, sizeof buf, "small%d", np);
     else snprintf(buf, sizeof buf, "generic");

@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import W, assert_fixed_equal, gen_fixed, result_to_numpy, seed_of
+from helpers import W, assert_fixed_equal, gen_fixed, masks_equal_up_to_cut_ties, result_to_numpy, seed_of
 
 pytestmark = pytest.mark.gpu
 
@@ -148,3 +148,26 @@ def test_obsolete_reliability_anchor(contract_vectors):
     assert int(r.rel1[0]) == v["expected"]["obsolete_rel1"] and int(r.rel2[0]) == v["expected"]["obsolete_rel2"]
     assert int(int(r.rel2[0]) / 1000) / 1000 == v["anchors"]["obsolete_rel2_3digits"]
     assert r.consensus[0].tolist() == v["expected"]["consensus"]       # everything else is unchanged
+
+
+@pytest.mark.parametrize("N,D,F", [(100, 3, 20), (256, 128, 51), (130, 40, 26)])
+def test_misaligned_wide_rounds_take_the_staged_fallback(N, D, F):
+    """Rounds that are not 16-byte aligned cannot use the global-tile kernel: the staged `wide` variant runs."""
+    import svoc
+    from oracle import cref
+    rng = np.random.default_rng(seed_of(N, D, F, "misaligned"))
+    T = 12 if N * D > 8192 else 60
+    x = gen_fixed("colluders", rng, T, N, D).astype(np.int32)
+    big = torch.from_numpy(np.concatenate([np.zeros(1, np.int32), x.reshape(-1)])).cuda()
+    view = big[1:].view(T, N, D)
+    assert view.data_ptr() % 16 != 0
+    r = result_to_numpy(svoc.consensus_fixed(view, F))
+    assert_fixed_equal(r, cref.fixed_batch(x.astype(np.int64), F, True, 0, True), T, label="misaligned wide")
+    rf = svoc.consensus_float(view.float() * 1e-6, F)     # aligned copy: the default wide kernel
+    rm = svoc.consensus_float((big.float() * 1e-6)[1:].view(T, N, D), F)
+    # the two float kernels sum qr in different orders: flags may differ only for rows within rounding of the cut
+    same = masks_equal_up_to_cut_ties(rf.reliable.cpu().numpy(), rm.reliable.cpu().numpy(),
+                                      rf.qr.double().cpu().numpy(), N, F, 1e-4)
+    assert same.mean() > 0.7
+    sel = torch.from_numpy(same).cuda()
+    torch.testing.assert_close(rf.consensus[sel], rm.consensus[sel], rtol=1e-6, atol=1e-7)
