@@ -137,3 +137,23 @@ def test_contract_mirror_reverts_on_panic():
     with pytest.raises(ContractPanic):
         c.update_prediction([1, 2, 3])                               # wrong dimension
     assert c.get_consensus_value() == [0, 0]
+
+
+def test_integration_md_ctypes_stub_runs(golden):
+    """The numpy-only ctypes stub printed in INTEGRATION.md is executed as written."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "INTEGRATION.md")).read()
+    code = re.search(r"```python\n(.*?)```", text, flags=re.S).group(1)
+    ns = {}
+    cwd = os.getcwd()
+    os.chdir(root)
+    try:
+        exec(code, ns)
+        key = "n20_d2_f4"
+        mask, cons = ns["identify_and_consensus"](golden[key + "_pred"], 4)
+    finally:
+        os.chdir(cwd)
+    assert np.array_equal(mask, golden[key + "_mask"])
+    np.testing.assert_allclose(cons, golden[key + "_consensus"], rtol=1e-12)
