@@ -428,7 +428,7 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
 
 // ------------------------------------------------------------------------------ the kernel
 template <class Tr, int NPAD>
-__global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) consensus_kernel(const Params p) {
+__global__ void __launch_bounds__(NPAD == 0 ? 256 : 128, NPAD == 64 ? 3 : 1) consensus_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
