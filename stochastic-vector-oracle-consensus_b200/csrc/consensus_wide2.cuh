@@ -11,7 +11,10 @@
 //     128 KB tile two CTAs — two rounds — share an SM and fill each other's stalls;
 //   * the key scale comes from a 64-row sample of the column (values outside it clamp to the end
 //     buckets, which keeps keys monotone), saving one sweep.
-// A CTA-wide barrier is needed only where rows meet columns (4 per round).
+//   * which rows are kept is found by EVERY warp on its own, from the shared risk array (7-bit keys of the
+//     risks in registers, SWAR bisection with warp reductions, exact ranking of the cut bucket): all warps
+//     get the same answer, so the column phase that follows needs no barrier and no exchange.
+// A CTA-wide barrier is needed only where rows meet columns (2 per round; 4 when the all-pairs ranking runs).
 // Reference semantics: see consensus_kernel.cuh (contract.cairo:442-503 etc.).
 #pragma once
 #include <type_traits>
@@ -22,6 +25,16 @@ namespace svoc {
 
 constexpr int W2_THREADS = 512;
 constexpr int W2_CAP = 32;
+constexpr int W2_RCAP = 32;          // rows of the cut bucket one warp ranks exactly (one per lane)
+#ifndef W2_SELECT_FAST
+#define W2_SELECT_FAST 1
+#endif
+#ifndef W2_NARROW
+#define W2_NARROW 0
+#endif
+#ifndef W2_SPAN
+#define W2_SPAN 3
+#endif
 
 struct W2Ctx {
     int N, D, RP;          // rows, dimensions, rows per part (multiple of 32)
@@ -122,7 +135,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
             else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
         }
         // ---- the window: the bucket of rank klo alone when rank khi is inside it, else that and the next two
-        const unsigned span = (khi < LE) ? 1u : 3u;
+        const unsigned span = (khi < LE) ? 1u : (unsigned)W2_SPAN;
         const unsigned up = prefix + span > 127u ? 127u : prefix + span;
         const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
         // flags of this part's rows, RP/32 words (compile-time count when RPT is given)
@@ -164,16 +177,26 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
         in_t thr = const_value;
         uint32_t kmin = 0xffffffffu, kmax = 0u;
         if (m <= W2_CAP) {
-            // values of this part's window rows -> slots off.., loads issued back to back
+            // values of this part's window rows -> slots off..  Four loads are issued before the first value is
+            // stored: one L2 round trip per four rows instead of one per row
             int k = off;
 #pragma unroll
             for (int g = 0; g < (RPT ? RPT : 512); g += 32) {
                 unsigned acc = fl[g / 32];
                 while (acc) {
-                    const int pos = __ffs(acc) - 1;
-                    acc &= acc - 1;
-                    lc[k * WD] = tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c];
-                    ++k;
+                    in_t v[4];
+                    bool on[4];
+                    const int pos0 = __ffs(acc) - 1;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        on[u] = acc != 0u;
+                        const int pos = on[u] ? __ffs(acc) - 1 : pos0;   // idle slots re-read a valid row
+                        acc &= acc - 1;
+                        v[u] = tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c];
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (on[u]) lc[(k++) * WD] = v[u];
                 }
             }
             __syncwarp(w.cmask);
@@ -247,12 +270,22 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
             }
         }
         if (rescue) {                             // rank khi lies above the window: smallest flagged value above it
+            // sixteen independent loads per trip (the flags are applied afterwards): a dependent chain of 64
+            // L2 round trips here would hold the whole CTA at its next barrier
             uint32_t best = 0xffffffffu;
             const in_t *ptr = tile + row_lo * WD + w.c;
-            for (int row = row_lo; row < row_hi; ++row, ptr += WD) {
-                if (keep && !keep[row]) continue;
-                const in_t x = *ptr;
-                if (x > thr) { const uint32_t kx = okey(x); best = kx < best ? kx : best; }
+            for (int row = row_lo; row < row_hi; row += 16, ptr += 16 * WD) {
+                in_t x[16];
+#pragma unroll
+                for (int k = 0; k < 16; ++k) x[k] = (row + k < row_hi) ? ptr[k * WD] : thr;
+                uint4 kf = make_uint4(0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u);
+                if (keep) kf = *reinterpret_cast<const uint4 *>(keep + row);      // row is a multiple of 16
+                const unsigned kw4[4] = {kf.x, kf.y, kf.z, kf.w};
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const bool on = (kw4[k >> 2] >> (8 * (k & 3))) & 0xffu;
+                    if (on && x[k] > thr) { const uint32_t kx = okey(x[k]); best = kx < best ? kx : best; }
+                }
             }
             best = col_reduce(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
             unkey(best, v_hi);
@@ -260,6 +293,156 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
         break;
     }
     return Tr::half_sum((val_t)v_lo, (val_t)v_hi);
+}
+
+// Which rows are kept: the R rows that come first under (risk asc, index desc | asc) — contract.cairo:470-486
+// drops the tail of that order.  Run by ONE warp (the others wait at the next barrier and leave the SM to
+// the co-resident CTA); all-pairs counting over 16 warps costs about 25 times the instructions.
+// Lane l holds the rows j*32 + l (j < NS) in q[].  A level works on the still undecided rows: 7-bit monotone
+// keys over their exact range — linear in the BIT PATTERN of the float image of the risk, i.e. piecewise
+// logarithmic in its value, because the kept rows usually form a narrow cluster far below the dropped
+// ones — packed four per register; bisection over the key bits for the bucket of the cut (SWAR counting as
+// in count_ge, one warp reduction per bit).  Rows in lower buckets are kept, rows in higher ones dropped,
+// the cut bucket stays undecided: if it holds at most W2_RCAP rows they are ranked exactly, one per lane;
+// if all its rows are equal the index order decides; else the next level re-keys it over its own range.
+// Returns false when the risks are negative / non-finite or the levels run out: the caller then runs the
+// all-pairs ranking.  words[j] = kept rows j*32 .. j*32+31 (same value in every lane).
+template <class acc_t, int NS>
+__device__ __forceinline__ bool w2_select_rows(const acc_t (&q)[NS], int N, int R, bool high, acc_t *wq, int *wi,
+                                               unsigned *ww, unsigned (&words)[NS]) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned below_me = (1u << lane) - 1u;
+    constexpr int NW = (NS + 3) / 4;
+    constexpr int NB = 32 * 4 * NW;                  // key bytes in the warp, sentinels included
+    unsigned bits[NS];
+    unsigned cand = 0, kept = 0;                     // slot masks of this lane: undecided / kept
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+        bits[j] = __float_as_uint((float)q[j]);      // monotone image (rounding keeps order); ties are settled on q
+        if (j * 32 + lane < N) cand |= 1u << j;
+    }
+    int m = N, need = R;                             // undecided rows, and how many of them are kept
+    bool done = false;
+#pragma unroll 1
+    for (int level = 0; level < 8 && !done; ++level) {
+        unsigned bmin = 0xffffffffu, bmax = 0u;
+#pragma unroll
+        for (int j = 0; j < NS; ++j)
+            if ((cand >> j) & 1u) {
+                bmin = bits[j] < bmin ? bits[j] : bmin;
+                bmax = bits[j] > bmax ? bits[j] : bmax;
+            }
+        bmin = __reduce_min_sync(full, bmin);
+        bmax = __reduce_max_sync(full, bmax);
+        if (bmax >= 0x7f800000u) return false;       // sign bit, inf, nan: non-negative finite floats order like their bits
+        if (bmax == bmin) {
+            if constexpr (!std::is_floating_point<acc_t>::value) {
+                // equal images need not be equal integers: check
+                const unsigned first = __ballot_sync(full, cand != 0);
+                acc_t ref = 0;
+#pragma unroll
+                for (int j = NS - 1; j >= 0; --j)
+                    if ((cand >> j) & 1u) ref = q[j];
+                ref = __shfl_sync(full, ref, __ffs(first) - 1);
+                bool same = true;
+#pragma unroll
+                for (int j = 0; j < NS; ++j)
+                    if ((cand >> j) & 1u) same &= q[j] == ref;
+                if (!__all_sync(full, same)) return false;
+            }
+            // equal risks: the index order decides (rows are held in index order: slot-major, then lane)
+            int base = 0;
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                const bool c = (cand >> j) & 1u;
+                const unsigned bal = __ballot_sync(full, c);
+                const int pos = base + __popc(bal & below_me);
+                if (c && (high ? pos >= m - need : pos < need)) kept |= 1u << j;
+                base += __popc(bal);
+            }
+            done = true;
+            break;
+        }
+        const float inv = 1.0f / (float)(bmax - bmin);
+        unsigned key[NS], kw[NW];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+            const float t = __saturatef((float)(bits[j] - bmin) * inv);
+            key[j] = ((cand >> j) & 1u) ? (__float_as_uint(__fmaf_rn(t, 126.0f, 8388608.0f)) & 0xffu) : 127u;
+        }
+        int sk = 0;
+#pragma unroll
+        for (int g = 0; g < NW; ++g) {
+            kw[g] = pack4(key[4 * g], 4 * g + 1 < NS ? key[4 * g + 1] : 127u, 4 * g + 2 < NS ? key[4 * g + 2] : 127u,
+                          4 * g + 3 < NS ? key[4 * g + 3] : 127u);
+            sk = (int)__dp4a(kw[g], 0x01010101u, (unsigned)sk);
+        }
+        sk = __reduce_add_sync(full, sk);
+        const int k = need - 1;
+        unsigned prefix = 0;
+        int L = 0, LE = m;
+#pragma unroll
+        for (int bit = 6; bit >= 0; --bit) {
+            const unsigned pv = prefix | (1u << bit);
+            const unsigned cb = (128u - pv) * 0x01010101u;
+            int acc = 0;
+#pragma unroll
+            for (int g = 0; g < NW; ++g) acc = __dp4a((int)(kw[g] + cb), 0x01010101, acc);
+            acc = __reduce_add_sync(full, acc);
+            const int lt = NB - ((sk + NB * (int)(128u - pv) - acc) >> 8);
+            if (lt <= k) { prefix = pv; L = lt; }
+            else LE = lt;
+        }
+        unsigned next = 0;
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+            if (key[j] < prefix) kept |= 1u << j;
+            if (key[j] == prefix) next |= 1u << j;
+        }
+        cand = next;
+        m = LE - L;
+        need -= L;
+        if (need == m) {                              // the cut falls on the bucket's end
+            kept |= cand;
+            done = true;
+        } else if (m <= W2_RCAP) {
+            // compact the cut bucket's rows (index order) into the list; lane t ranks entry t among them
+            int base = 0;
+#pragma unroll
+            for (int j = 0; j < NS; ++j) {
+                const bool c = (cand >> j) & 1u;
+                const unsigned bal = __ballot_sync(full, c);
+                if (c) {
+                    const int pos = base + __popc(bal & below_me);
+                    wq[pos] = q[j];
+                    wi[pos] = j * 32 + lane;
+                }
+                base += __popc(bal);
+            }
+            if (lane < NS) ww[lane] = 0u;
+            __syncwarp();
+            const int t = lane < m ? lane : 0;
+            const acc_t qv = wq[t];
+            const int iv = wi[t];
+            int before = 0;
+            for (int b = 0; b < m; ++b) {
+                const acc_t qb = wq[b];
+                const int ib = wi[b];
+                before += (qb < qv) | ((qb == qv) & (high ? ib > iv : ib < iv));
+            }
+            if (lane < m && before < need) atomicOr(&ww[iv >> 5], 1u << (iv & 31));
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < NS; ++j) kept |= ((ww[j] >> lane) & 1u) << j;
+            __syncwarp();                             // the list is reused by the next round
+            done = true;
+        }
+    }
+    if (!done) return false;
+#pragma unroll
+    for (int j = 0; j < NS; ++j) words[j] = __ballot_sync(full, (kept >> j) & 1u);
+    return true;
 }
 
 template <class Tr, int DT, int PT, int RPT>
@@ -278,9 +461,12 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
     in_t *list = reinterpret_cast<in_t *>(smem_raw + off);      off += al((size_t)W2_CAP * D * sizeof(in_t));
     val_t *c1 = reinterpret_cast<val_t *>(smem_raw + off);      off += al((size_t)D * sizeof(val_t));
     acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + off);    off += al((size_t)N * sizeof(acc_t));
-    acc_t *red_s = reinterpret_cast<acc_t *>(smem_raw + off);   off += al((size_t)2 * (W2_THREADS / 32) * sizeof(acc_t));
+    acc_t *wq = reinterpret_cast<acc_t *>(smem_raw + off);      off += al((size_t)W2_RCAP * sizeof(acc_t));
+    int *wi = reinterpret_cast<int *>(smem_raw + off);          off += al((size_t)W2_RCAP * sizeof(int));
+    unsigned *ww = reinterpret_cast<unsigned *>(smem_raw + off); off += 64;
     uint32_t *maskw = reinterpret_cast<uint32_t *>(smem_raw + off); off += al((size_t)(P * RP / 32 + 1) * 4);
     int *stw_s = reinterpret_cast<int *>(smem_raw + off);       off += 16;
+    int *sel_s = stw_s + 1;
     uint8_t *keep_s = smem_raw + off;
 
     // column units: lane = part * CW + column-in-warp, CW = 32 / P columns per warp
@@ -326,8 +512,21 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
                 lo = vmin(lo, x);
                 hi = vmax(hi, x);
             }
+            // The scale spans [largest of the parts' sample minima, smallest of their maxima] — roughly the
+            // central three quarters of the column — so the buckets around the median are about twice as fine
+            // as over the full range.  Values outside clamp to the end buckets (keys stay monotone); a centre
+            // that falls into an end bucket just meets a crowded window there and is resolved by re-keying.
+#if W2_NARROW
+            if (ns == 0) {                       // a part without rows must not narrow the range
+                lo = std::numeric_limits<in_t>::lowest();
+                hi = std::numeric_limits<in_t>::max();
+            }
+            lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmax(a, b); });
+            hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmin(a, b); });
+#else
             lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
             hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+#endif
             if (!(hi > lo)) {                    // degenerate sample: exact sweep, which also detects a constant column
                 const in_t *q = tile + row_lo * D + w.c;
                 for (int row = row_lo; row < min(N, row_lo + RP); ++row, q += D) {
@@ -424,126 +623,136 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
         if (tid == 0 && r + gridDim.x < p.T)
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(tile + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
 
-        // ---- phase 3: rank of every row under (qr asc, index desc | asc); the HR lanes of a row split the
-        //      comparison range and add up by shuffle.  One compare per pair outside the warp's own rows.
+        // ---- phase 3: which rows are kept.  Warp 0 works it out alone (w2_select_rows) while the others wait;
+        //      the all-pairs ranking — rank of every row under (qr asc, index desc | asc), rows spread over all
+        //      warps — runs when ranks are an output or the selection gives up on this round's risks.
         {
+            constexpr int NS = (PT && RPT) ? (PT * RPT) / 32 : 16;
             const bool high = p.tie == SVOC_TIE_HIGH_INDEX_KEPT;
-            for (int ib = warp * RW; ib < N; ib += (W2_THREADS / 32) * RW) {
-                const int i = ib + (lane - rh * RW);
-                const bool ok = i < N;
-                const acc_t mine = qr_s[ok ? i : 0];
-                const int i1 = min(N, ib + RW);             // the warp's rows are [ib, i1)
-                const int jh = (((N + HR - 1) / HR) + 3) & ~3, jlo = rh * jh, jhi = min(N, jlo + jh);
-                int tie = 0;
-                // [jlo, jhi) minus the warp's own rows: one compare per pair, strict on one side of the warp's
-                // rows and non-strict on the other
-                auto count = [&](auto strict, int a, int b) {
-                    int c = 0, j = a;
-                    auto hit = [&](acc_t q) {
-                        if constexpr (sizeof(acc_t) == 4) {      // set.{lt,le}.s32.f32: 0 or -1 in one instruction
-                            int d;
-                            float qf, mf;
-                            memcpy(&qf, &q, 4);
-                            memcpy(&mf, &mine, 4);
-                            if constexpr (decltype(strict)::value) asm("set.lt.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(qf), "f"(mf));
-                            else asm("set.le.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(qf), "f"(mf));
-                            return -d;
-                        } else {
-                            if constexpr (decltype(strict)::value) return q < mine ? 1 : 0;
-                            else return q <= mine ? 1 : 0;
-                        }
-                    };
-                    if constexpr (sizeof(acc_t) == 4) {
-                        for (; j < b && (j & 3); ++j) c += hit(qr_s[j]);
-                        for (; j + 4 <= b; j += 4) {
-                            const float4 v = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(qr_s) + j);
-                            acc_t q0, q1, q2, q3;
-                            memcpy(&q0, &v.x, 4); memcpy(&q1, &v.y, 4); memcpy(&q2, &v.z, 4); memcpy(&q3, &v.w, 4);
-                            c += (hit(q0) + hit(q1)) + (hit(q2) + hit(q3));
-                        }
-                    }
-                    for (; j < b; ++j) c += hit(qr_s[j]);
-                    return c;
-                };
-                const int a_end = min(jhi, max(jlo, ib)), b_beg = max(jlo, min(jhi, i1));
-                int rank = high ? count(std::true_type{}, jlo, a_end) + count(std::false_type{}, b_beg, jhi)
-                                : count(std::false_type{}, jlo, a_end) + count(std::true_type{}, b_beg, jhi);
-                for (int j = a_end; j < b_beg; ++j) {
-                    const acc_t q = qr_s[j];
-                    tie += (q < mine ? 1 : 0) + (((q == mine) & (high ? j > i : j < i)) ? 1 : 0);
-                }
-                rank += tie;
-                if (HR >= 2) rank += __shfl_xor_sync(0xffffffffu, rank, RW);
-                if (HR >= 4) rank += __shfl_xor_sync(0xffffffffu, rank, 2 * RW);
-                if (ok && rh == 0) {
-                    keep_s[i] = rank < R ? 1 : 0;
-                    if (p.rank) p.rank[(size_t)r * N + i] = rank;
-                }
-            }
-        }
-        __syncthreads();
-        // ---- mask words and the two sums
-        {
-            const int nw = (P * RP) / 32;
-            for (int k = tid; k < nw; k += W2_THREADS) {
-                uint32_t bits = 0;
-                const uint32_t *kw = reinterpret_cast<const uint32_t *>(keep_s + k * 32);
-                if (k * 32 + 32 <= N) {
+            unsigned words[NS];
+            acc_t qrow[NS];
+            if (warp == 0) {
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        const uint32_t v = kw[q];     // four flag bytes (0 / 1)
-                        bits |= ((v & 1u) | ((v >> 7) & 2u) | ((v >> 14) & 4u) | ((v >> 21) & 8u)) << (4 * q);
+                for (int j = 0; j < NS; ++j) qrow[j] = (j * 32 + lane < N) ? qr_s[j * 32 + lane] : acc_t(0);
+                bool fast = W2_SELECT_FAST && p.rank == nullptr;
+                if (fast) fast = w2_select_rows<acc_t, NS>(qrow, N, R, high, wq, wi, ww, words);
+                if (fast) {
+#pragma unroll
+                    for (int j = 0; j < NS; ++j) {
+                        if (j * 32 + lane < N) keep_s[j * 32 + lane] = (words[j] >> lane) & 1u;
+                        if (lane == j && j * 32 < P * RP) maskw[j] = words[j];
                     }
-                } else {
-                    for (int b = 0; b < 32 && k * 32 + b < N; ++b) bits |= (uint32_t)(keep_s[k * 32 + b] != 0) << b;
                 }
-                maskw[k] = bits;
-                if (p.reliable && k < p.words) p.reliable[(size_t)r * p.words + k] = bits;
+                if (lane == 0) *sel_s = fast ? 1 : 0;
             }
-            acc_t s1 = 0, s2 = 0;
-            for (int i = tid; i < N; i += W2_THREADS) {
-                const acc_t q = qr_s[i];
-                s1 += q;
-                if (keep_s[i]) s2 += q;
-            }
-            for (int o = 16; o; o >>= 1) {
-                s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-                s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-            }
-            if (lane == 0) { red_s[warp] = s1; red_s[W2_THREADS / 32 + warp] = s2; }
-        }
-        __syncthreads();
-        if (tid == 0) {
-            acc_t s1 = 0, s2 = 0;
-            for (int k = 0; k < W2_THREADS / 32; ++k) { s1 += red_s[k]; s2 += red_s[W2_THREADS / 32 + k]; }
-            int stw = STW_OK;
-            if constexpr (Tr::fixed) {
-                const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
-                if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
-                i64 rel2 = 0;
-                if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-                else {
-                    rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
-                    if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+            __syncthreads();
+            if (!*sel_s) {
+                for (int ib = warp * RW; ib < N; ib += (W2_THREADS / 32) * RW) {
+                    const int i = ib + (lane - rh * RW);
+                    const bool ok = i < N;
+                    const acc_t mine = qr_s[ok ? i : 0];
+                    const int i1 = min(N, ib + RW);             // the warp's rows are [ib, i1)
+                    const int jh = (((N + HR - 1) / HR) + 3) & ~3, jlo = rh * jh, jhi = min(N, jlo + jh);
+                    int tie = 0;
+                    // [jlo, jhi) minus the warp's own rows: one compare per pair, strict on one side of the warp's
+                    // rows and non-strict on the other
+                    auto count = [&](auto strict, int a, int b) {
+                        int c = 0, j = a;
+                        auto hit = [&](acc_t q) {
+                            if constexpr (sizeof(acc_t) == 4) {      // set.{lt,le}.s32.f32: 0 or -1 in one instruction
+                                int d;
+                                float qf, mf;
+                                memcpy(&qf, &q, 4);
+                                memcpy(&mf, &mine, 4);
+                                if constexpr (decltype(strict)::value) asm("set.lt.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(qf), "f"(mf));
+                                else asm("set.le.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(qf), "f"(mf));
+                                return -d;
+                            } else {
+                                if constexpr (decltype(strict)::value) return q < mine ? 1 : 0;
+                                else return q <= mine ? 1 : 0;
+                            }
+                        };
+                        if constexpr (sizeof(acc_t) == 4) {
+                            for (; j < b && (j & 3); ++j) c += hit(qr_s[j]);
+                            for (; j + 4 <= b; j += 4) {
+                                const float4 v = *reinterpret_cast<const float4 *>(reinterpret_cast<const float *>(qr_s) + j);
+                                acc_t q0, q1, q2, q3;
+                                memcpy(&q0, &v.x, 4); memcpy(&q1, &v.y, 4); memcpy(&q2, &v.z, 4); memcpy(&q3, &v.w, 4);
+                                c += (hit(q0) + hit(q1)) + (hit(q2) + hit(q3));
+                            }
+                        }
+                        for (; j < b; ++j) c += hit(qr_s[j]);
+                        return c;
+                    };
+                    const int a_end = min(jhi, max(jlo, ib)), b_beg = max(jlo, min(jhi, i1));
+                    int rank = high ? count(std::true_type{}, jlo, a_end) + count(std::false_type{}, b_beg, jhi)
+                                    : count(std::false_type{}, jlo, a_end) + count(std::true_type{}, b_beg, jhi);
+                    for (int j = a_end; j < b_beg; ++j) {
+                        const acc_t q = qr_s[j];
+                        tie += (q < mine ? 1 : 0) + (((q == mine) & (high ? j > i : j < i)) ? 1 : 0);
+                    }
+                    rank += tie;
+                    if (HR >= 2) rank += __shfl_xor_sync(0xffffffffu, rank, RW);
+                    if (HR >= 4) rank += __shfl_xor_sync(0xffffffffu, rank, 2 * RW);
+                    if (ok && rh == 0) {
+                        keep_s[i] = rank < R ? 1 : 0;
+                        if (p.rank) p.rank[(size_t)r * N + i] = rank;
+                    }
                 }
-                reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
-                reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
-            } else {
-                const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
-                if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
-                val_t rel2 = 0;
-                if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-                else {
-                    rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
-                    if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
+                __syncthreads();
+                if (warp == 0) {
+#pragma unroll
+                    for (int j = 0; j < NS; ++j) {
+                        words[j] = __ballot_sync(0xffffffffu, j * 32 + lane < N && keep_s[j * 32 + lane]);
+                        if (lane == j && j * 32 < P * RP) maskw[j] = words[j];
+                    }
                 }
-                reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
-                reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
+                __syncthreads();
             }
-            if (stw != STW_OK) atomicMin(stw_s, stw);
-            if (!p.want_moments) {   // nothing later contributes to the status: publish it now
-                const int sw = *stw_s;
-                p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+            // ---- the round's scalars: warp 0, while the others start on their columns
+            if (warp == 0) {
+                acc_t s1 = 0, s2 = 0;
+#pragma unroll
+                for (int j = 0; j < NS; ++j) {
+                    s1 += qrow[j];
+                    if ((words[j] >> lane) & 1u) s2 += qrow[j];
+                    if (p.reliable && lane == j && j < p.words) p.reliable[(size_t)r * p.words + j] = words[j];
+                }
+                for (int o = 16; o; o >>= 1) {
+                    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+                }
+                if (lane == 0) {
+                    int stw = STW_OK;
+                    if constexpr (Tr::fixed) {
+                        const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
+                        if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
+                        i64 rel2 = 0;
+                        if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                        else {
+                            rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
+                            if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+                        }
+                        reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
+                        reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
+                    } else {
+                        const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
+                        if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
+                        val_t rel2 = 0;
+                        if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                        else {
+                            rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
+                            if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
+                        }
+                        reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
+                        reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
+                    }
+                    if (stw != STW_OK) atomicMin(stw_s, stw);
+                    if (!p.want_moments) {   // nothing later contributes to the status: publish it now
+                        const int sw = *stw_s;
+                        p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+                    }
+                }
             }
         }
         // ---- phase 4: second-pass centre over the reliable rows (+ moments)
@@ -607,7 +816,9 @@ inline size_t wide2_smem_bytes(int N, int D, int P, int RP, int CS, size_t es, s
     s += al((size_t)W2_CAP * D * es);
     s += al((size_t)D * vs);
     s += al((size_t)N * vs);
-    s += al((size_t)2 * (W2_THREADS / 32) * vs);
+    s += al((size_t)W2_RCAP * vs);
+    s += al((size_t)W2_RCAP * 4);
+    s += 64;
     s += al((size_t)(P * RP / 32 + 1) * 4);
     s += 16;
     s += al((size_t)N);
