@@ -397,7 +397,8 @@ def main():
                    "per_step": "consensus kernel + stats accumulation" + (" + NCCL allreduce of the stats buffer" if world > 1 else "")},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes": T * B,
-                     "peak_source": peak_src, "bytes_per_round": B, "kernel_ms": kms},
+                     "peak_source": peak_src, "bytes_per_round": B, "kernel_ms": kms,
+                     "kernel_ms_per_step": [round(v, 3) for v in kern_ms]},
         "e2e": {"value": e2e_value, "unit": "rounds/s", "h2d_bytes_per_step": e2e_T * N * D * s_in,
                 "d2h_bytes_per_step": d2h, "sample_rounds_per_step": e2e_T, "steps": e2e_steps,
                 "api": "svoc.consensus_%s_host -> svoc_consensus_%s_host (C ABI, pinned host buffers)" % (("fixed",) * 2 if wl["dtype"] == "i32" else ("float",) * 2)},

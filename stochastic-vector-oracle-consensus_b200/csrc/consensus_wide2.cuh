@@ -355,10 +355,10 @@ __device__ __forceinline__ bool w2_select_rows(const acc_t (&q)[NS], int N, int 
             int base = 0;
 #pragma unroll
             for (int j = 0; j < NS; ++j) {
-                const bool c = (cand >> j) & 1u;
-                const unsigned bal = __ballot_sync(full, c);
+                const unsigned c = (cand >> j) & 1u;
+                const unsigned bal = __ballot_sync(full, c != 0u);
                 const int pos = base + __popc(bal & below_me);
-                if (c && (high ? pos >= m - need : pos < need)) kept |= 1u << j;
+                kept |= (c & (unsigned)(high ? pos >= m - need : pos < need)) << j;
                 base += __popc(bal);
             }
             done = true;
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
     uint8_t *keysT = smem_raw + off;                            off += al((size_t)D * CS);
     in_t *list = reinterpret_cast<in_t *>(smem_raw + off);      off += al((size_t)W2_CAP * D * sizeof(in_t));
     val_t *c1 = reinterpret_cast<val_t *>(smem_raw + off);      off += al((size_t)D * sizeof(val_t));
-    acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + off);    off += al((size_t)N * sizeof(acc_t));
+    acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + off);    off += al((size_t)P * RP * sizeof(acc_t));
     acc_t *wq = reinterpret_cast<acc_t *>(smem_raw + off);      off += al((size_t)W2_RCAP * sizeof(acc_t));
     int *wi = reinterpret_cast<int *>(smem_raw + off);          off += al((size_t)W2_RCAP * sizeof(int));
     unsigned *ww = reinterpret_cast<unsigned *>(smem_raw + off); off += 64;
@@ -557,14 +557,18 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
             for (int i0 = 4 * warp; i0 < N; i0 += 4 * (W2_THREADS / 32)) {
                 acc_t q[4] = {0, 0, 0, 0};
                 bool bad = false;
-                for (int d = 4 * lane; d < D; d += 128) {
+                // one row pointer per trip, opaque to the compiler: it would otherwise rebuild the 64-bit round
+                // offset in front of every load
+                const in_t *rp = tile + (size_t)i0 * D + 4 * lane;
+                asm volatile("" : "+l"(rp));
+                for (int d = 4 * lane; d < D; d += 128, rp += 128) {
                     val_t cc[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) cc[k] = c1[d + k];
                     int4 xv[4];
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
-                        xv[u] = (i0 + u < N) ? *reinterpret_cast<const int4 *>(tile + (size_t)(i0 + u) * D + d) : make_int4(0, 0, 0, 0);
+                        xv[u] = (i0 + u < N) ? *reinterpret_cast<const int4 *>(rp + u * D) : make_int4(0, 0, 0, 0);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         in_t x[4];
@@ -633,14 +637,22 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
             acc_t qrow[NS];
             if (warp == 0) {
 #pragma unroll
-                for (int j = 0; j < NS; ++j) qrow[j] = (j * 32 + lane < N) ? qr_s[j * 32 + lane] : acc_t(0);
+                for (int j = 0; j < NS; ++j)          // qr_s has P*RP entries; rows >= N are masked out by the selection
+                    qrow[j] = (j * 32 < P * RP) ? qr_s[j * 32 + lane] : acc_t(0);
                 bool fast = W2_SELECT_FAST && p.rank == nullptr;
                 if (fast) fast = w2_select_rows<acc_t, NS>(qrow, N, R, high, wq, wi, ww, words);
                 if (fast) {
+                    unsigned mine = 0;
 #pragma unroll
-                    for (int j = 0; j < NS; ++j) {
-                        if (j * 32 + lane < N) keep_s[j * 32 + lane] = (words[j] >> lane) & 1u;
-                        if (lane == j && j * 32 < P * RP) maskw[j] = words[j];
+                    for (int j = 0; j < NS; ++j) mine = lane == j ? words[j] : mine;
+                    if (lane * 32 < P * RP) maskw[lane] = mine;
+                    __syncwarp();
+                    // flag bytes, eight rows per lane and trip: bit b of a mask byte -> byte b (0 / 1)
+                    for (int g = lane; g * 8 < P * RP; g += 32) {
+                        const unsigned bits8 = (maskw[g >> 2] >> (8 * (g & 3))) & 0xffu;
+                        const unsigned lo4 = ((bits8 & 0xfu) * 0x00204081u) & 0x01010101u;
+                        const unsigned hi4 = ((bits8 >> 4) * 0x00204081u) & 0x01010101u;
+                        *reinterpret_cast<uint2 *>(keep_s + 8 * g) = make_uint2(lo4, hi4);
                     }
                 }
                 if (lane == 0) *sel_s = fast ? 1 : 0;
@@ -711,13 +723,17 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
             }
             // ---- the round's scalars: warp 0, while the others start on their columns
             if (warp == 0) {
+                // risks and mask words are read back from shared memory: nothing stays live across the barrier
                 acc_t s1 = 0, s2 = 0;
 #pragma unroll
                 for (int j = 0; j < NS; ++j) {
-                    s1 += qrow[j];
-                    if ((words[j] >> lane) & 1u) s2 += qrow[j];
-                    if (p.reliable && lane == j && j < p.words) p.reliable[(size_t)r * p.words + j] = words[j];
+                    if (j * 32 + lane < N) {
+                        const acc_t qv = qr_s[j * 32 + lane];
+                        s1 += qv;
+                        if ((maskw[j] >> lane) & 1u) s2 += qv;
+                    }
                 }
+                if (p.reliable && lane < p.words) p.reliable[(size_t)r * p.words + lane] = maskw[lane];
                 for (int o = 16; o; o >>= 1) {
                     s1 += __shfl_xor_sync(0xffffffffu, s1, o);
                     s2 += __shfl_xor_sync(0xffffffffu, s2, o);
@@ -815,13 +831,13 @@ inline size_t wide2_smem_bytes(int N, int D, int P, int RP, int CS, size_t es, s
     s += al((size_t)D * CS);
     s += al((size_t)W2_CAP * D * es);
     s += al((size_t)D * vs);
-    s += al((size_t)N * vs);
+    s += al((size_t)P * RP * vs);
     s += al((size_t)W2_RCAP * vs);
     s += al((size_t)W2_RCAP * 4);
     s += 64;
     s += al((size_t)(P * RP / 32 + 1) * 4);
     s += 16;
-    s += al((size_t)N);
+    s += al((size_t)P * RP);
     return s;
 }
 
