@@ -58,39 +58,67 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 100)."""
+    """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 100).
+    The process is started BEFORE the warm-up steps and the timed region only begins once its first sample has
+    arrived: nvidia-smi's start-up (NVML initialisation) can stall a running kernel for ~100 ms, which must not
+    land inside the timed steps.  `with sampler:` brackets the timed region; only samples that arrived inside
+    it are summarised."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
-        self.index, self.proc, self.rows = index, None, []
+        self.index, self.proc, self.rows, self.t0, self.t1 = index, None, [], None, None
+        self._lock = threading.Lock()
 
-    def __enter__(self):
+    def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            time.sleep(0.25)   # let the first sample land before the timed region starts
+            threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
         return self
 
+    def _read(self):
+        for line in self.proc.stdout:
+            if line.strip():
+                with self._lock:
+                    self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def wait_first(self, timeout=10.0):
+        end = time.time() + timeout
+        while self.proc is not None and time.time() < end:
+            with self._lock:
+                if self.rows:
+                    return
+            time.sleep(0.02)
+
+    def __enter__(self):
+        if self.proc is None:
+            self.start()
+        self.wait_first()
+        self.t0 = time.time()
+        return self
+
     def __exit__(self, *a):
+        self.t1 = time.time()
         if self.proc is None:
             return
-        time.sleep(0.15)
+        time.sleep(0.12)            # one more sample for very short regions
         self.proc.terminate()
         try:
-            out, _ = self.proc.communicate(timeout=5)
+            self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-            out = ""
-        self.rows = [[c.strip() for c in line.split(",")] for line in out.strip().splitlines() if line.strip()]
 
     def summary(self):
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        with self._lock:
+            rows = list(self.rows)
+        inside = [r for t, r in rows if self.t0 is not None and self.t0 <= t <= (self.t1 or t) + 0.15]
+        for r in (inside or [r for _, r in rows]):
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
                 for n, v in zip(names, r[2:6]):
@@ -227,12 +255,13 @@ def fused_arm(args, wl, torch, svoc, dist, dev, rank, world, local):
         st.allreduce()
         return st
 
+    clk = ClockSampler(local).start()      # started before the warm-up, see the class comment
     for _ in range(max(3, args.warmup)):
         svoc.montecarlo(max(1, (hi - lo) // 64), N, D, F, a=10.0, b=15.0, seed=1, trial_offset=lo, dtype=torch.float32, device=dev).allreduce()
     barrier()
     l0 = svoc.launch_count()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
+    with clk:
         a.record()
         for _ in range(args.steps):
             st = step()
@@ -330,13 +359,14 @@ def main():
             stats.allreduce()
         return r
 
+    clk = ClockSampler(local).start()      # started before the warm-up, see the class comment
     for _ in range(max(3, args.warmup)):
         step()
     barrier()
     l0 = svoc.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 2)]
     kern_ms = []
-    with ClockSampler(local) as clk:
+    with clk:
         ev[0].record()
         for i in range(args.steps):
             ev[2 * i + 1].record()

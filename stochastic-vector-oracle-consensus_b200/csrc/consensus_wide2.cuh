@@ -11,10 +11,10 @@
 //     128 KB tile two CTAs — two rounds — share an SM and fill each other's stalls;
 //   * the key scale comes from a 64-row sample of the column (values outside it clamp to the end
 //     buckets, which keeps keys monotone), saving one sweep.
-//   * which rows are kept is found by EVERY warp on its own, from the shared risk array (7-bit keys of the
-//     risks in registers, SWAR bisection with warp reductions, exact ranking of the cut bucket): all warps
-//     get the same answer, so the column phase that follows needs no barrier and no exchange.
-// A CTA-wide barrier is needed only where rows meet columns (2 per round; 4 when the all-pairs ranking runs).
+//   * which rows are kept is found by ONE warp from the shared risk array (7-bit keys of the
+//     risks in registers, SWAR bisection with warp reductions, exact ranking of the cut bucket) while the
+//     other warps wait at the next barrier; all-pairs counting over all warps is the fallback.
+// A CTA-wide barrier is needed only where rows meet columns (3 per round; 5 when the all-pairs ranking runs).
 // Reference semantics: see consensus_kernel.cuh (contract.cairo:442-503 etc.).
 #pragma once
 #include <type_traits>
@@ -28,12 +28,6 @@ constexpr int W2_CAP = 32;
 constexpr int W2_RCAP = 32;          // rows of the cut bucket one warp ranks exactly (one per lane)
 #ifndef W2_SELECT_FAST
 #define W2_SELECT_FAST 1
-#endif
-#ifndef W2_NARROW
-#define W2_NARROW 0
-#endif
-#ifndef W2_SPAN
-#define W2_SPAN 3
 #endif
 
 struct W2Ctx {
@@ -135,7 +129,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
             else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
         }
         // ---- the window: the bucket of rank klo alone when rank khi is inside it, else that and the next two
-        const unsigned span = (khi < LE) ? 1u : (unsigned)W2_SPAN;
+        const unsigned span = (khi < LE) ? 1u : 3u;
         const unsigned up = prefix + span > 127u ? 127u : prefix + span;
         const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
         // flags of this part's rows, RP/32 words (compile-time count when RPT is given)
@@ -512,21 +506,8 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
                 lo = vmin(lo, x);
                 hi = vmax(hi, x);
             }
-            // The scale spans [largest of the parts' sample minima, smallest of their maxima] — roughly the
-            // central three quarters of the column — so the buckets around the median are about twice as fine
-            // as over the full range.  Values outside clamp to the end buckets (keys stay monotone); a centre
-            // that falls into an end bucket just meets a crowded window there and is resolved by re-keying.
-#if W2_NARROW
-            if (ns == 0) {                       // a part without rows must not narrow the range
-                lo = std::numeric_limits<in_t>::lowest();
-                hi = std::numeric_limits<in_t>::max();
-            }
-            lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmax(a, b); });
-            hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmin(a, b); });
-#else
             lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
             hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
-#endif
             if (!(hi > lo)) {                    // degenerate sample: exact sweep, which also detects a constant column
                 const in_t *q = tile + row_lo * D + w.c;
                 for (int row = row_lo; row < min(N, row_lo + RP); ++row, q += D) {
