@@ -149,3 +149,73 @@ def test_rank_output_and_threshold_search_agree(N, D, F):
         step = idx[:, 1:] - idx[:, :-1]
         assert torch.all(step[same] < 0) if tie == svoc.TIE_HIGH_INDEX_KEPT else torch.all(step[same] > 0)
         assert same.any()
+
+
+def _selection_inputs(kind, T, N, D, rng):
+    """Rounds built to reach every branch of the single-warp row selection of the wide variant."""
+    if kind == "cluster":        # 90 % of the rows within 1e-4 of each other, the rest far away: the cut bucket of
+        x = 0.5 + 1e-4 * rng.standard_normal((T, N, D))   # the first level holds > 32 distinct risks -> second level
+        far = rng.random((T, N)) < 0.1
+        x = np.where(far[:, :, None], rng.random((T, N, D)), x)
+    elif kind == "ties":         # groups of identical rows of random sizes: exact ties of every size at the cut
+        base = rng.beta(10, 15, (T, 8, D))
+        x = base[:, rng.integers(0, 8, N), :]
+    elif kind == "two_values":   # every risk is one of two values
+        a, b = rng.random((T, 1, D)), rng.random((T, 1, D))
+        x = np.where(rng.random((T, N, 1)) < 0.5, a, b)
+    elif kind == "constant":     # all risks equal: the index order alone decides
+        x = np.broadcast_to(rng.random((T, 1, D)), (T, N, D)).copy()
+    elif kind == "spread":       # risks over many orders of magnitude
+        x = 0.5 + rng.standard_normal((T, N, D)) * (10.0 ** rng.uniform(-6, -1, (T, N, 1)))
+    else:
+        raise ValueError(kind)
+    return np.clip(x, 0.0, 1.0)
+
+
+@pytest.mark.parametrize("kind", ["cluster", "ties", "two_values", "constant", "spread"])
+@pytest.mark.parametrize("N,D", [(256, 128), (130, 40), (512, 8)])
+def test_row_selection_matches_all_pairs_ranking(kind, N, D):
+    """want_rank=True ranks every row by all-pairs counting; want_rank=False runs the bisection-based selection.
+    Same flags, consensus and reliabilities for both tie rules, both dtypes and cuts from 0 to N-2 dropped rows."""
+    import svoc
+    rng = np.random.default_rng(seed_of(kind, N, D))
+    T = 24
+    x = _selection_inputs(kind, T, N, D, rng)
+    for F in (0, 1, N // 5, N // 2, N - 33, N - 2):
+        for tie in (svoc.TIE_HIGH_INDEX_KEPT, svoc.TIE_LOW_INDEX_KEPT):
+            t = torch.from_numpy(x.astype(np.float32)).cuda()
+            a = svoc.consensus_float(t, F, tie_rule=tie, want_rank=True)
+            b = svoc.consensus_float(t, F, tie_rule=tie, want_rank=False)
+            assert torch.equal(a.reliable_words, b.reliable_words), (kind, F, tie, "f32")
+            assert torch.equal(a.consensus, b.consensus) and torch.equal(a.status, b.status)
+            torch.testing.assert_close(a.rel2, b.rel2, rtol=1e-5, atol=1e-6)
+            assert torch.all(b.reliable.sum(dim=1) == N - F)
+            # fixed-point form on the same rounds: risks are 64-bit integers, selected through their float images
+            ti = torch.from_numpy((x * 1e6).astype(np.int32)).cuda()
+            ai = svoc.consensus_fixed(ti, F, constrained=True, tie_rule=tie, want_rank=True)
+            bi = svoc.consensus_fixed(ti, F, constrained=True, tie_rule=tie, want_rank=False)
+            assert torch.equal(ai.reliable_words, bi.reliable_words), (kind, F, tie, "i32")
+            assert torch.equal(ai.consensus, bi.consensus) and torch.equal(ai.rel2, bi.rel2) and torch.equal(ai.status, bi.status)
+
+
+def _equal_image_rounds(T, N, D, rng):
+    x = np.full((T, N, D), 900000, dtype=np.int64)
+    x[:, ::2, :] = 100000                          # centre 500000: every risk is about 128 * 0.16 wsad = 2.05e7 > 2^24
+    x[:, :, 0] += rng.integers(0, 3, (T, N))       # risks that differ by one or two units
+    return x
+
+
+def test_row_selection_with_equal_float_images_of_integer_risks():
+    """Fixed-point risks above 2^24 that differ by a few units share a float image: more than 32 such rows at the
+    cut cannot be settled on the images, and the kernel must fall back to exact all-pairs ranking."""
+    import svoc
+    T, N, D, F = 16, 256, 128, 100
+    x = _equal_image_rounds(T, N, D, np.random.default_rng(5))
+    t = torch.from_numpy(x.astype(np.int32)).cuda()
+    for tie in (svoc.TIE_HIGH_INDEX_KEPT, svoc.TIE_LOW_INDEX_KEPT):
+        a = svoc.consensus_fixed(t, F, constrained=True, tie_rule=tie, want_rank=True)
+        b = svoc.consensus_fixed(t, F, constrained=True, tie_rule=tie, want_rank=False)
+        assert torch.equal(a.reliable_words, b.reliable_words)
+        assert torch.equal(a.consensus, b.consensus) and torch.equal(a.rel2, b.rel2)
+        q0 = a.qr[0]
+        assert int(q0.min()) > (1 << 24) and len(torch.unique(q0)) > len(torch.unique(q0.float()))
