@@ -6,6 +6,7 @@ from .engine import (WSAD, ConsensusResult, consensus_fixed, consensus_fixed_hos
                      consensus_float_host, expected_reliability, kernel_variant, rank_array)
 
 from .workload import Generated, RunningStats, generate, montecarlo  # noqa: F401
+from .replay import EpochReplay, replay_epochs  # noqa: F401
 from . import client, contract, distributed, notebook  # noqa: F401,E402
 
 __version__ = "0.1.0"

@@ -58,6 +58,65 @@ def from_hex(x: str) -> int:
     return int(x, 16)
 
 
+# ---- wire format ---------------------------------------------------------------
+# A deployment exchanges felt252 words: a wsad value v is sent as v (v >= 0) or v + P (v < 0); a FeltVector is a
+# Cairo Array<felt252>, serialised as its length followed by its elements.  The batched forms below work on
+# whole arrays so that engine inputs / outputs can be compared with, or fed to, a real contract.
+
+def float_to_wsad_array(x) -> np.ndarray:
+    """`int(x * 1e6)` of client/contract.py:48-53 and ipynb beta :250-251 on a whole array: float64 product,
+    truncation toward zero, as int64.  Accepts numpy arrays and torch tensors (CPU or CUDA; returns the same kind)."""
+    if isinstance(x, torch.Tensor):
+        return torch.trunc(x.to(torch.float64) * 1e6).to(torch.int64)
+    return np.trunc(np.asarray(x, dtype=np.float64) * 1e6).astype(np.int64)
+
+
+def wsad_to_float_array(v):
+    """`float(v) * 1e-6` of client/contract.py:41-45 on a whole array of (already signed) wsad integers."""
+    if isinstance(v, torch.Tensor):
+        return v.to(torch.float64) * 1e-6
+    return np.asarray(v, dtype=np.int64).astype(np.float64) * 1e-6
+
+
+def wsad_array_to_felts(v) -> list:
+    """Signed wsad integers (any shape, numpy or torch) -> nested lists of felt252 Python ints (`as_felt`,
+    contract/src/math.cairo:22-35: negatives become v + P)."""
+    a = v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v)
+    conv = np.frompyfunc(lambda t: i128_to_felt(int(t)), 1, 1)
+    return conv(a.astype(object)).tolist()
+
+
+def felts_to_wsad_array(felts) -> np.ndarray:
+    """Nested lists of felt252 ints (or 0x.. strings) -> int64 array of signed wsad values (`as_wsad`,
+    math.cairo:37-50; raises if a value does not fit 64 bits, which no constrained prediction does)."""
+    def one(t):
+        t = from_hex(t) if isinstance(t, str) else int(t)
+        s = felt_to_i128(t)
+        if not -(1 << 63) <= s < (1 << 63):
+            raise OverflowError(f"wsad value {s} does not fit int64")
+        return s
+    conv = np.frompyfunc(one, 1, 1)
+    return conv(np.asarray(felts, dtype=object)).astype(np.int64)
+
+
+def update_prediction_calldata(prediction) -> List[int]:
+    """Calldata of `update_prediction(prediction: FeltVector)` (contract.cairo:588) for one oracle: the array
+    length, then one felt per component.  `prediction` holds floats (client side, oracle_scheduler.py:150-166)."""
+    felts = [float_to_fwsad(float(x)) for x in prediction]
+    return [len(felts)] + felts
+
+
+def constructor_calldata(admins, enable_oracle_replacement, required_majority, n_failing_oracles, constrained,
+                         unconstrained_max_spread, dimension, oracles) -> List[int]:
+    """Constructor calldata in the order of contract/README.md:40-66 / contract.cairo:235-247: admins span, five
+    scalars (the spread as a felt-encoded wsad), the dimension, oracles span."""
+    as_int = lambda a: from_hex(a) if isinstance(a, str) else int(a)     # noqa: E731
+    return ([len(admins)] + [as_int(a) for a in admins]
+            + [int(bool(enable_oracle_replacement)), int(required_majority), int(n_failing_oracles), int(bool(constrained)),
+               i128_to_felt(int(unconstrained_max_spread)), int(dimension)]
+            + [len(oracles)] + [as_int(o) for o in oracles])
+
+
 def gen_oracles_predictions(sentiment_analysis: List[np.ndarray]) -> List[np.ndarray]:
     """client/oracle_scheduler.py:73-92: the first N_FAILING_ORACLES oracles are uniform noise, the others
     a bootstrap mean of BOOTSTRAPING_SUBSET rows of the sentiment window; then shuffled.  Host-side data

@@ -1,6 +1,7 @@
 """GPU: the name-compatible mirrors of the reference's Python functions and of the contract ABI."""
 import numpy as np
 import pytest
+import torch
 
 from helpers import ranks_equal_up_to_ties
 
@@ -157,3 +158,47 @@ def test_integration_md_ctypes_stub_runs(golden):
         os.chdir(cwd)
     assert np.array_equal(mask, golden[key + "_mask"])
     np.testing.assert_allclose(cons, golden[key + "_consensus"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("kind", ["beta", "tiny"])
+def test_batched_epoch_replay_matches_sequential_contract(kind):
+    """an epoch of N update_prediction calls replayed as one batch gives, after every commit,
+    what the contract mirror computes one transaction at a time — including reverted commits ('tiny' rounds hit
+    the sqrt(1) / division-by-zero panics of math.cairo:271-292, 320-338)."""
+    import numpy as np
+    import svoc
+    from svoc.client import i128_to_felt
+    from svoc.contract import ContractPanic, OracleConsensusNDS
+    from helpers import gen_fixed
+    rng = np.random.default_rng(11)
+    E, N, D, F = 6, 7, 3, 2
+    prev = gen_fixed("beta", rng, E, N, D)
+    new = gen_fixed(kind, rng, E, N, D)
+    order = np.stack([rng.permutation(N) for _ in range(E)])
+    rp = svoc.replay_epochs(torch.from_numpy(prev).cuda(), torch.from_numpy(new).cuda(), F, constrained=True,
+                            order=torch.from_numpy(order).cuda())
+    n_reverts = 0
+    for e in range(E):
+        c = OracleConsensusNDS(["adm"], False, 1, F, True, 0, D, [f"o{i}" for i in range(N)])
+        for i in range(N):                                   # bring the mirror to the state before the epoch
+            try:
+                c.update_prediction([i128_to_felt(int(v)) for v in prev[e, i]], caller=f"o{i}")
+            except ContractPanic:
+                pytest.skip("the previous-epoch state itself panics")
+        for k in range(N):
+            i = int(order[e, k])
+            try:
+                c.update_prediction([i128_to_felt(int(v)) for v in new[e, i]], caller=f"o{i}")
+                assert not bool(rp.reverted[e, k])
+            except ContractPanic as ex:
+                n_reverts += 1
+                assert bool(rp.reverted[e, k]) and int(rp.revert_status[e, k]) == ex.status
+            got = rp.after_commit(e, k)
+            if got:
+                assert int(got["rel1"]) == c.reliability_first_pass and int(got["rel2"]) == c.reliability_second_pass
+                assert got["consensus"].tolist() == c.consensus_value
+                assert got["reliable"].tolist() == c.reliable
+    if kind == "tiny":
+        assert n_reverts > 0 and rp.passes > 1
+    else:
+        assert rp.passes == 1

@@ -123,3 +123,29 @@ def test_world_size_2_allreduce_equals_single_rank(tmp_path):
     assert got["counts"][528:535].tolist() == (~o["reliable"][ok]).sum(axis=0).tolist()
     assert got["counts"][535:542].tolist() == o["qr"][ok].sum(axis=0).tolist()
     assert abs(float(got["sums"][0]) - float(o["rel1"][ok].sum()) * 1e-6) < 1e-6
+
+
+def test_wire_format_codecs():
+    """felt252 <-> wsad codecs and calldata layouts (client/contract.py:35-53,
+    contract/src/math.cairo:22-50, tests/test_math.cairo:95-96, contract/README.md:40-66)."""
+    import numpy as np
+    from svoc import client as c
+    P = c.UPPER_BOUND_FELT252
+    assert c.felt_to_i128(P - 1) == -1 and c.i128_to_felt(-1) == P - 1          # test_math.cairo:95-96
+    x = np.array([[0.0, 0.4999999, 0.5, 1.0], [-0.25, -1e-7, 0.123456789, 20.714]])
+    w = c.float_to_wsad_array(x)
+    assert w.tolist() == [[int(v * 1e6) for v in row] for row in x.tolist()]      # truncation toward zero
+    felts = c.wsad_array_to_felts(w)
+    assert felts[1][0] == P - 250000 and felts[0][3] == 1000000
+    assert [[c.float_to_fwsad(v) for v in row] for row in x.tolist()] == felts      # the scalar client helper
+    back = c.felts_to_wsad_array(felts)
+    assert back.dtype == np.int64 and np.array_equal(back, w)
+    assert np.array_equal(c.felts_to_wsad_array([[c.to_hex(f) for f in row] for row in felts]), w)
+    np.testing.assert_allclose(c.wsad_to_float_array(back), np.trunc(x * 1e6) * 1e-6)
+    assert [c.fwsad_to_float(f) for f in felts[1]] == c.wsad_to_float_array(back)[1].tolist()
+    import torch
+    assert torch.equal(c.float_to_wsad_array(torch.from_numpy(x)), torch.from_numpy(w))
+    assert c.update_prediction_calldata([0.5, 0.25]) == [2, 500000, 250000]
+    cd = c.constructor_calldata(["0x1", "0x2", "0x3"], True, 2, 2, True, 0, 6, list(range(10, 17)))
+    assert cd == [3, 1, 2, 3, 1, 2, 2, 1, 0, 6, 7, 10, 11, 12, 13, 14, 15, 16]        # contract/README.md:40-66
+    assert c.constructor_calldata([5], False, 1, 0, False, -3, 1, [9])[6] == P - 3
