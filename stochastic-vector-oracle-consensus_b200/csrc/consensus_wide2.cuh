@@ -760,14 +760,20 @@ __global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Pa
                     if (refined1) {
                         w2_build_keys<Tr, true, DT, RPT>(w, tile, keep_s, lo, hi, sc);
                     } else {
-                        for (int g = 0; g < RP; g += 32) {   // dropped rows of this part -> sentinel key
-                            const int base = row_lo + g;
-                            unsigned drop = ~maskw[base >> 5];
-                            if (base + 32 > N) drop &= (base < N) ? ((1u << (N - base)) - 1u) : 0u;
-                            while (drop) {
-                                const int b = __ffs(drop) - 1;
-                                drop &= drop - 1;
-                                w.mykeys[g + b] = 127;
+                        // dropped rows of this part -> sentinel key.  Branch-free: four drop bits are spread to
+                        // the low bits of four bytes (one multiply), scaled to 0x7f and OR-ed into the key word
+                        // (keys are <= 127, and rows >= N already hold the sentinel)
+#pragma unroll
+                        for (int g = 0; g < (RPT ? RPT : 512); g += 32) {
+                            if (g < RP) {
+                                const unsigned drop = ~maskw[(row_lo + g) >> 5];
+                                uint4 a = *reinterpret_cast<const uint4 *>(w.mykeys + g);
+                                uint4 b = *reinterpret_cast<const uint4 *>(w.mykeys + g + 16);
+                                auto sent = [&](int j) { return ((((drop >> (4 * j)) & 0xfu) * 0x00204081u) & 0x01010101u) * 0x7fu; };
+                                a.x |= sent(0); a.y |= sent(1); a.z |= sent(2); a.w |= sent(3);
+                                b.x |= sent(4); b.y |= sent(5); b.z |= sent(6); b.w |= sent(7);
+                                *reinterpret_cast<uint4 *>(w.mykeys + g) = a;
+                                *reinterpret_cast<uint4 *>(w.mykeys + g + 16) = b;
                             }
                         }
                     }
