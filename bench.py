@@ -58,7 +58,10 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 100).
+    """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 250:
+    about one query in sixty stalls the running kernel for 30-100 ms on these boxes — measured with
+    tools/hiccup.sh, 0 slow steps in 80 without the sampler — so the period is kept as long as a short timed
+    region allows).
     The process is started BEFORE the warm-up steps and the timed region only begins once its first sample has
     arrived: nvidia-smi's start-up (NVML initialisation) can stall a running kernel for ~100 ms, which must not
     land inside the timed steps.  `with sampler:` brackets the timed region; only samples that arrived inside
@@ -72,8 +75,11 @@ class ClockSampler:
 
     def start(self):
         try:
+            if os.environ.get("SVOC_BENCH_SAMPLER_MS") == "0":       # diagnostics only: no sampler at all
+                raise RuntimeError("sampler disabled")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms",
+                                          os.environ.get("SVOC_BENCH_SAMPLER_MS", "250")],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -105,7 +111,7 @@ class ClockSampler:
         self.t1 = time.time()
         if self.proc is None:
             return
-        time.sleep(0.12)            # one more sample for very short regions
+        time.sleep(0.26)            # one more sample for very short regions
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)

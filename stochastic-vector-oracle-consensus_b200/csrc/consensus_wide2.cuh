@@ -23,7 +23,11 @@
 
 namespace svoc {
 
-constexpr int W2_THREADS = 512;
+#ifndef W2_THREADS_N
+#define W2_THREADS_N 512
+#endif
+constexpr int W2_THREADS = W2_THREADS_N;
+constexpr int W2_CTAS_PER_SM = 1024 / W2_THREADS;
 constexpr int W2_CAP = 32;
 constexpr int W2_RCAP = 32;          // rows of the cut bucket one warp ranks exactly (one per lane)
 #ifndef W2_SELECT_FAST
@@ -440,7 +444,7 @@ __device__ __forceinline__ bool w2_select_rows(const acc_t (&q)[NS], int N, int 
 }
 
 template <class Tr, int DT, int PT, int RPT>
-__global__ void __launch_bounds__(W2_THREADS, 2) consensus_wide2_kernel(const Params p) {
+__global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
@@ -831,8 +835,12 @@ inline size_t wide2_smem_bytes(int N, int D, int P, int RP, int CS, size_t es, s
 template <class Tr>
 int launch_wide2(const Params &p, const Plan &pl, cudaStream_t st) {
     void (*kern)(const Params) = consensus_wide2_kernel<Tr, 0, 0, 0>;
+#if W2_THREADS_N == 512
     if (p.D == 128 && p.wP == 4 && p.wRP == 64) kern = consensus_wide2_kernel<Tr, 128, 4, 64>;
     else if (p.D == 128 && p.wP == 4) kern = consensus_wide2_kernel<Tr, 128, 4, 0>;
+#else
+    if (p.D == 128 && p.wP == 2 && p.wRP == 128) kern = consensus_wide2_kernel<Tr, 128, 2, 128>;
+#endif
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, W2_THREADS, pl.smem, st>>>(p);

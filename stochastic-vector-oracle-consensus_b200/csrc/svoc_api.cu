@@ -118,7 +118,7 @@ static bool plan_wide2(const svoc_config &c, const void *pred, Plan &pl) {
 static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
     Plan pl{};
     if (plan_wide2(c, pred, pl)) {
-        pl.grid = std::min<long long>(T, (long long)sm_count() * 2);
+        pl.grid = std::min<long long>(T, (long long)sm_count() * W2_CTAS_PER_SM);
         return pl;
     }
     if (forced_variant() != "generic" && plan_wide(c, pred, pl)) {
