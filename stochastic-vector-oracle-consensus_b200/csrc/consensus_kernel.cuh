@@ -322,30 +322,29 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
         // constrained fixed form: every qr is at most D * 1e6, so when that fits 32 bits the low words decide
         bool low32 = false;
         if constexpr (Tr::fixed) low32 = p.constrained && (u64)D * (u64)WSAD < 0xffffffffull;
+        // One compare per pair: risks are non-negative, so their bit patterns order like unsigned integers
+        // (float, double and int64 alike), and "equal, but ahead by the index rule" is folded into the
+        // threshold: row j comes before row i iff bits(q_j) < bits(q_i) + [j wins a tie against i].
+        auto count = [&](auto zero, const auto *qb, int stride, int i) {
+            using UT = decltype(zero);
+            const UT mine = qb[stride * i];
+            int rank = 0;
+            if (high) {
+#pragma unroll 4
+                for (int j = 0; j < N; ++j) rank += qb[stride * j] < (UT)(mine + (UT)(j > i ? 1 : 0)) ? 1 : 0;
+            } else {
+#pragma unroll 4
+                for (int j = 0; j < N; ++j) rank += qb[stride * j] < (UT)(mine + (UT)(j < i ? 1 : 0)) ? 1 : 0;
+            }
+            return rank;
+        };
         for (int w = tid; w < nr * N; w += nt) {
             const int r = w / N, i = w - r * N;
             const acc_t *q = qr_s + (size_t)r * N;
-            int rank = 0;
-            if (low32) {
-                const uint32_t *q32 = reinterpret_cast<const uint32_t *>(q);
-                const uint32_t mine = q32[2 * i];
-                int eq = 0;
-                for (int j = 0; j < N; ++j) {
-                    const uint32_t v = q32[2 * j];
-                    rank += v < mine ? 1 : 0;
-                    eq += ((v == mine) & (high ? j > i : j < i)) ? 1 : 0;
-                }
-                rank += eq;
-            } else {
-                const acc_t mine = q[i];
-                int eq = 0;
-                for (int j = 0; j < N; ++j) {
-                    const acc_t v = q[j];
-                    rank += v < mine ? 1 : 0;
-                    eq += ((v == mine) & (high ? j > i : j < i)) ? 1 : 0;
-                }
-                rank += eq;
-            }
+            int rank;
+            if (low32) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), 2, i);
+            else if constexpr (sizeof(acc_t) == 4) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), 1, i);
+            else rank = count(u64(0), reinterpret_cast<const u64 *>(q), 1, i);
             keep_s[w] = rank < R ? 1 : 0;
             if (p.rank) p.rank[(size_t)(r0 - ob) * N + w] = rank;
         }

@@ -105,6 +105,12 @@ __host__ __device__ __forceinline__ void cswap(T &a, T &b) {
     a = lo;
     b = hi;
 }
+// fp32: two FMNMX instead of a compare and two selects
+__host__ __device__ __forceinline__ void cswap(float &a, float &b) {
+    const float lo = fminf(a, b), hi = fmaxf(a, b);
+    a = lo;
+    b = hi;
+}
 
 // The comparator list is built at compile time and applied through an index sequence so
 // that every array index is a constant expression (plain unrolled loops left the array in
