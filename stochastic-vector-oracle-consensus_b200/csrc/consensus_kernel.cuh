@@ -325,26 +325,44 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
         // One compare per pair: risks are non-negative, so their bit patterns order like unsigned integers
         // (float, double and int64 alike), and "equal, but ahead by the index rule" is folded into the
         // threshold: row j comes before row i iff bits(q_j) < bits(q_i) + [j wins a tie against i].
-        auto count = [&](auto zero, const auto *qb, int stride, int i) {
+        // Both the threshold and the count ride on the carry flag (IADD3 with carry-out, IADD3.X with carry-in):
+        // four integer instructions and a load per pair.  After sub.cc the flag is the carry of x + ~y + 1, i.e.
+        // [x >= y] (NOT the borrow), so the loop counts the rows that do NOT come before row i.
+        auto count = [&](auto zero, const auto *qb, auto stride_c, int i) {
             using UT = decltype(zero);
+            constexpr int stride = decltype(stride_c)::value;
             const UT mine = qb[stride * i];
-            int rank = 0;
-            if (high) {
+            int ge = 0;
+            auto step = [&](UT v, int x, int y) {                  // ge += v >= mine + [x >= y]
+                if constexpr (sizeof(UT) == 4) {
+                    asm("{\n\t.reg .u32 t, thr;\n\tsub.cc.u32 t, %2, %3;\n\taddc.u32 thr, %4, 0;\n\t"
+                        "sub.cc.u32 t, %1, thr;\n\taddc.u32 %0, %0, 0;\n\t}"
+                        : "+r"(ge) : "r"((uint32_t)v), "r"(x), "r"(y), "r"((uint32_t)mine));
+                } else {
+                    asm("{\n\t.reg .u32 t, tl, th;\n\tsub.cc.u32 t, %3, %4;\n\taddc.cc.u32 tl, %5, 0;\n\taddc.u32 th, %6, 0;\n\t"
+                        "sub.cc.u32 t, %1, tl;\n\tsubc.cc.u32 t, %2, th;\n\taddc.u32 %0, %0, 0;\n\t}"
+                        : "+r"(ge)
+                        : "r"((uint32_t)v), "r"((uint32_t)((u64)v >> 32)), "r"(x), "r"(y), "r"((uint32_t)mine),
+                          "r"((uint32_t)((u64)mine >> 32)));
+                }
+            };
+            if (high) {                                            // the tie goes to the higher index: j >= i + 1
 #pragma unroll 4
-                for (int j = 0; j < N; ++j) rank += qb[stride * j] < (UT)(mine + (UT)(j > i ? 1 : 0)) ? 1 : 0;
-            } else {
+                for (int j = 0; j < N; ++j) step(qb[stride * j], j, i + 1);
+            } else {                                               // ... to the lower index: i >= j + 1
 #pragma unroll 4
-                for (int j = 0; j < N; ++j) rank += qb[stride * j] < (UT)(mine + (UT)(j < i ? 1 : 0)) ? 1 : 0;
+                for (int j = 0; j < N; ++j) step(qb[stride * j], i, j + 1);
             }
+            const int rank = N - ge;
             return rank;
         };
         for (int w = tid; w < nr * N; w += nt) {
             const int r = w / N, i = w - r * N;
             const acc_t *q = qr_s + (size_t)r * N;
             int rank;
-            if (low32) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), 2, i);
-            else if constexpr (sizeof(acc_t) == 4) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), 1, i);
-            else rank = count(u64(0), reinterpret_cast<const u64 *>(q), 1, i);
+            if (low32) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), std::integral_constant<int, 2>{}, i);
+            else if constexpr (sizeof(acc_t) == 4) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), std::integral_constant<int, 1>{}, i);
+            else rank = count(u64(0), reinterpret_cast<const u64 *>(q), std::integral_constant<int, 1>{}, i);
             keep_s[w] = rank < R ? 1 : 0;
             if (p.rank) p.rank[(size_t)(r0 - ob) * N + w] = rank;
         }
