@@ -77,9 +77,32 @@ __device__ __forceinline__ float draw_component(const svoc_gen_config &c, bool i
         return atanf(mu + b * normal_from(r.v[0], r.v[1])) * 0.318309886183791f + 0.5f;
     }
     if (c.law == SVOC_LAW_BETA) {
-        const float ga = gamma_draw(a, t_lo, t_hi, slot, iter, k0, k1);
-        iter = 0x40000000u;
-        const float gb = gamma_draw(b, t_lo, t_hi, slot, iter, k0, k1);
+        // First attempt of both gammas from ONE Philox call: the two Box-Muller branches (cosine, sine) are
+        // independent normals, words 2 and 3 the two squeeze uniforms.  Marsaglia-Tsang accepts ~95 % of the
+        // attempts for alpha >= 1, so the per-gamma loops below (fresh counters) run for about one draw in ten.
+        float ga = -1.0f, gb = -1.0f;
+        if (a >= 1.0f && b >= 1.0f) {
+            const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0x20000000u, k0, k1);
+            const float rad = sqrtf(-2.0f * __logf(u01(r.v[0])));
+            float sn, cs;
+            __sincosf(6.2831853071795864f * u01(r.v[1]), &sn, &cs);
+            auto attempt = [](float alpha, float x, float u) {
+                const float d = alpha - 1.0f / 3.0f, cc = rsqrtf(9.0f * d);
+                float v = 1.0f + cc * x;
+                if (v <= 0.0f) return -1.0f;
+                v = v * v * v;
+                const float x2 = x * x;
+                if (u < 1.0f - 0.0331f * x2 * x2 || logf(u) < 0.5f * x2 + d * (1.0f - v + logf(v))) return d * v;
+                return -1.0f;
+            };
+            ga = attempt(a, rad * cs, u01(r.v[2]));
+            gb = attempt(b, rad * sn, u01(r.v[3]));
+        }
+        if (ga < 0.0f) ga = gamma_draw(a, t_lo, t_hi, slot, iter, k0, k1);
+        if (gb < 0.0f) {
+            iter = 0x40000000u;
+            gb = gamma_draw(b, t_lo, t_hi, slot, iter, k0, k1);
+        }
         return ga / (ga + gb);
     }
     const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0, k0, k1);
