@@ -265,6 +265,40 @@ __device__ inline F reliability_float(F avg_qr, const Params &p) {
 // ------------------------------------------------------------------------------ one block of rounds
 // Phases 1-4 for the `nr` rounds staged at `tile` (row-major [nr][N][D]).  Outputs of round r0 + r go
 // to index (r0 - ob + r) of the output arrays, so a caller may point them at a per-block scratch.
+// Rank of element i among the N unsigned keys qb[stride * j] under (key asc, index desc | asc): the number of
+// elements that come before it.  One compare per pair: "equal, but ahead by the index rule" is folded into the
+// threshold — element j comes before element i iff key_j < key_i + [j wins a tie against i].  Non-negative
+// floats, doubles and int64 order like their bit patterns, so the risks are passed as raw words.
+// Both the threshold and the count ride on the carry flag (IADD3 with carry-out, IADD3.X with carry-in): four
+// integer instructions and a load per pair.  After sub.cc the flag is the carry of x + ~y + 1, i.e. [x >= y]
+// (NOT the borrow), so the loop counts the elements that do NOT come before element i.
+template <class UT, int stride>
+__device__ __forceinline__ int rank_of(const UT *qb, int N, int i, bool high) {
+    const UT mine = qb[stride * i];
+    int ge = 0;
+    auto step = [&](UT v, int x, int y) {                  // ge += v >= mine + [x >= y]
+        if constexpr (sizeof(UT) == 4) {
+            asm("{\n\t.reg .u32 t, thr;\n\tsub.cc.u32 t, %2, %3;\n\taddc.u32 thr, %4, 0;\n\t"
+                "sub.cc.u32 t, %1, thr;\n\taddc.u32 %0, %0, 0;\n\t}"
+                : "+r"(ge) : "r"((uint32_t)v), "r"(x), "r"(y), "r"((uint32_t)mine));
+        } else {
+            asm("{\n\t.reg .u32 t, tl, th;\n\tsub.cc.u32 t, %3, %4;\n\taddc.cc.u32 tl, %5, 0;\n\taddc.u32 th, %6, 0;\n\t"
+                "sub.cc.u32 t, %1, tl;\n\tsubc.cc.u32 t, %2, th;\n\taddc.u32 %0, %0, 0;\n\t}"
+                : "+r"(ge)
+                : "r"((uint32_t)v), "r"((uint32_t)((u64)v >> 32)), "r"(x), "r"(y), "r"((uint32_t)mine),
+                  "r"((uint32_t)((u64)mine >> 32)));
+        }
+    };
+    if (high) {                                            // the tie goes to the higher index: j >= i + 1
+#pragma unroll 4
+        for (int j = 0; j < N; ++j) step(qb[stride * j], j, i + 1);
+    } else {                                               // ... to the lower index: i >= j + 1
+#pragma unroll 4
+        for (int j = 0; j < N; ++j) step(qb[stride * j], i, j + 1);
+    }
+    return N - ge;
+}
+
 template <class Tr, int NPAD>
 __device__ __forceinline__ void consensus_block(const Params &p, const typename Tr::in_t *tile, i64 r0, int nr, i64 ob,
                                                 typename Tr::val_t *c1, typename Tr::acc_t *qr_s, int *stw_s,
@@ -322,47 +356,13 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
         // constrained fixed form: every qr is at most D * 1e6, so when that fits 32 bits the low words decide
         bool low32 = false;
         if constexpr (Tr::fixed) low32 = p.constrained && (u64)D * (u64)WSAD < 0xffffffffull;
-        // One compare per pair: risks are non-negative, so their bit patterns order like unsigned integers
-        // (float, double and int64 alike), and "equal, but ahead by the index rule" is folded into the
-        // threshold: row j comes before row i iff bits(q_j) < bits(q_i) + [j wins a tie against i].
-        // Both the threshold and the count ride on the carry flag (IADD3 with carry-out, IADD3.X with carry-in):
-        // four integer instructions and a load per pair.  After sub.cc the flag is the carry of x + ~y + 1, i.e.
-        // [x >= y] (NOT the borrow), so the loop counts the rows that do NOT come before row i.
-        auto count = [&](auto zero, const auto *qb, auto stride_c, int i) {
-            using UT = decltype(zero);
-            constexpr int stride = decltype(stride_c)::value;
-            const UT mine = qb[stride * i];
-            int ge = 0;
-            auto step = [&](UT v, int x, int y) {                  // ge += v >= mine + [x >= y]
-                if constexpr (sizeof(UT) == 4) {
-                    asm("{\n\t.reg .u32 t, thr;\n\tsub.cc.u32 t, %2, %3;\n\taddc.u32 thr, %4, 0;\n\t"
-                        "sub.cc.u32 t, %1, thr;\n\taddc.u32 %0, %0, 0;\n\t}"
-                        : "+r"(ge) : "r"((uint32_t)v), "r"(x), "r"(y), "r"((uint32_t)mine));
-                } else {
-                    asm("{\n\t.reg .u32 t, tl, th;\n\tsub.cc.u32 t, %3, %4;\n\taddc.cc.u32 tl, %5, 0;\n\taddc.u32 th, %6, 0;\n\t"
-                        "sub.cc.u32 t, %1, tl;\n\tsubc.cc.u32 t, %2, th;\n\taddc.u32 %0, %0, 0;\n\t}"
-                        : "+r"(ge)
-                        : "r"((uint32_t)v), "r"((uint32_t)((u64)v >> 32)), "r"(x), "r"(y), "r"((uint32_t)mine),
-                          "r"((uint32_t)((u64)mine >> 32)));
-                }
-            };
-            if (high) {                                            // the tie goes to the higher index: j >= i + 1
-#pragma unroll 4
-                for (int j = 0; j < N; ++j) step(qb[stride * j], j, i + 1);
-            } else {                                               // ... to the lower index: i >= j + 1
-#pragma unroll 4
-                for (int j = 0; j < N; ++j) step(qb[stride * j], i, j + 1);
-            }
-            const int rank = N - ge;
-            return rank;
-        };
         for (int w = tid; w < nr * N; w += nt) {
             const int r = w / N, i = w - r * N;
             const acc_t *q = qr_s + (size_t)r * N;
             int rank;
-            if (low32) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), std::integral_constant<int, 2>{}, i);
-            else if constexpr (sizeof(acc_t) == 4) rank = count(uint32_t(0), reinterpret_cast<const uint32_t *>(q), std::integral_constant<int, 1>{}, i);
-            else rank = count(u64(0), reinterpret_cast<const u64 *>(q), std::integral_constant<int, 1>{}, i);
+            if (low32) rank = rank_of<uint32_t, 2>(reinterpret_cast<const uint32_t *>(q), N, i, high);
+            else if constexpr (sizeof(acc_t) == 4) rank = rank_of<uint32_t, 1>(reinterpret_cast<const uint32_t *>(q), N, i, high);
+            else rank = rank_of<u64, 1>(reinterpret_cast<const u64 *>(q), N, i, high);
             keep_s[w] = rank < R ? 1 : 0;
             if (p.rank) p.rank[(size_t)(r0 - ob) * N + w] = rank;
         }

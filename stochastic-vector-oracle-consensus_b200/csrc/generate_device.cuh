@@ -77,32 +77,36 @@ __device__ __forceinline__ float draw_component(const svoc_gen_config &c, bool i
         return atanf(mu + b * normal_from(r.v[0], r.v[1])) * 0.318309886183791f + 0.5f;
     }
     if (c.law == SVOC_LAW_BETA) {
-        // First attempt of both gammas from ONE Philox call: the two Box-Muller branches (cosine, sine) are
-        // independent normals, words 2 and 3 the two squeeze uniforms.  Marsaglia-Tsang accepts ~95 % of the
-        // attempts for alpha >= 1, so the per-gamma loops below (fresh counters) run for about one draw in ten.
-        float ga = -1.0f, gb = -1.0f;
         if (a >= 1.0f && b >= 1.0f) {
-            const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0x20000000u, k0, k1);
-            const float rad = sqrtf(-2.0f * __logf(u01(r.v[0])));
-            float sn, cs;
-            __sincosf(6.2831853071795864f * u01(r.v[1]), &sn, &cs);
-            auto attempt = [](float alpha, float x, float u) {
-                const float d = alpha - 1.0f / 3.0f, cc = rsqrtf(9.0f * d);
+            // Both gammas (Marsaglia-Tsang) advance together: ONE Philox call per trip gives the two Box-Muller
+            // branches (cosine, sine: independent normals) and the two squeeze uniforms.  A trip accepts ~97 % of
+            // its attempts, but a warp repeats it while ANY lane still misses a gamma — separate per-gamma
+            // retry loops, and the precise logf of the second test, cost a warp three times as much.
+            const float da = a - 1.0f / 3.0f, ca = rsqrtf(9.0f * da), db = b - 1.0f / 3.0f, cb = rsqrtf(9.0f * db);
+            auto attempt = [](float d, float cc, float x, float u) {
                 float v = 1.0f + cc * x;
                 if (v <= 0.0f) return -1.0f;
                 v = v * v * v;
                 const float x2 = x * x;
-                if (u < 1.0f - 0.0331f * x2 * x2 || logf(u) < 0.5f * x2 + d * (1.0f - v + logf(v))) return d * v;
+                if (u < 1.0f - 0.0331f * x2 * x2 || __logf(u) < 0.5f * x2 + d * (1.0f - v + __logf(v))) return d * v;
                 return -1.0f;
             };
-            ga = attempt(a, rad * cs, u01(r.v[2]));
-            gb = attempt(b, rad * sn, u01(r.v[3]));
+            float ga = -1.0f, gb = -1.0f;
+            for (uint32_t it = 0; it < 64u && (ga < 0.0f || gb < 0.0f); ++it) {
+                const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0x20000000u + it, k0, k1);
+                const float rad = sqrtf(-2.0f * __logf(u01(r.v[0])));
+                float sn, cs;
+                __sincosf(6.2831853071795864f * u01(r.v[1]), &sn, &cs);
+                if (ga < 0.0f) ga = attempt(da, ca, rad * cs, u01(r.v[2]));
+                if (gb < 0.0f) gb = attempt(db, cb, rad * sn, u01(r.v[3]));
+            }
+            ga = ga < 0.0f ? da : ga;             // 64 rejections in a row: never in practice
+            gb = gb < 0.0f ? db : gb;
+            return __fdividef(ga, ga + gb);
         }
-        if (ga < 0.0f) ga = gamma_draw(a, t_lo, t_hi, slot, iter, k0, k1);
-        if (gb < 0.0f) {
-            iter = 0x40000000u;
-            gb = gamma_draw(b, t_lo, t_hi, slot, iter, k0, k1);
-        }
+        const float ga = gamma_draw(a, t_lo, t_hi, slot, iter, k0, k1);
+        iter = 0x40000000u;
+        const float gb = gamma_draw(b, t_lo, t_hi, slot, iter, k0, k1);
         return ga / (ga + gb);
     }
     const Philox4 r = philox4x32_10(t_lo, t_hi, slot, 0, k0, k1);

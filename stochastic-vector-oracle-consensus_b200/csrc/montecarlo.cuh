@@ -69,10 +69,7 @@ __global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) montecarlo_kernel(const
         __syncthreads();
         for (int w = tid; w < nr * N; w += nt) {
             const int r = w / N, i = w - r * N;
-            const uint32_t *kk = keys + (size_t)r * N;
-            const uint32_t mine = kk[i];
-            int rank = 0;
-            for (int j = 0; j < N; ++j) rank += (kk[j] < mine || (kk[j] == mine && j < i)) ? 1 : 0;
+            const int rank = rank_of<uint32_t, 1>(keys + (size_t)r * N, N, i, false);   // ties: lower index first
             honest_s[w] = rank < F ? 0 : 1;
         }
         __syncthreads();
