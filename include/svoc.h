@@ -120,6 +120,24 @@ int svoc_consensus_fixed_host(const svoc_config *cfg, const void *pred, int64_t 
 int svoc_consensus_float_host(const svoc_config *cfg, const void *pred, int64_t n_rounds,
                               const svoc_outputs *out);
 
+/* svoc_consensus_float_host for callers that must not allocate device memory (no counterpart in
+ * the reference; it exists for hosts of this library, not for parity).  Same arguments, same
+ * results.  The two calls above grow a device staging cache with cudaMalloc; a plugin inside a
+ * process whose device memory is owned by someone else, code that runs after the memory map
+ * is frozen, or a latency-bound loop (cudaMalloc / cudaFree take driver-wide locks and may
+ * synchronise the device) cannot afford that.  This variant stages through a buffer built into
+ * the library image — SVOC_NOALLOC_SCRATCH_BYTES of device memory on every GPU that loads the
+ * library, held until the process exits — runs on the legacy default stream, and calls no
+ * allocator.  A batch whose predictions plus requested outputs (each area padded to 256 bytes)
+ * exceed that size is rejected with an error that says how many rounds fit.
+ * The buffer is shared by all calls on a device and keeps the last call's contents; nothing in it
+ * needs to be zero (every byte that is read was written earlier in the same call).  Calls that
+ * overlap on the GPU race: one thread at a time per device.  The first call on a device looks
+ * up the buffer's device address (cudaGetSymbolAddress); make it before any stream capture. */
+#define SVOC_NOALLOC_SCRATCH_BYTES (16u << 20)
+int svoc_consensus_float_host_noalloc(const svoc_config *cfg, const void *pred, int64_t n_rounds,
+                                      const svoc_outputs *out);
+
 /* 1 - 2*mean(|A - median(A)|) over each flattened [N*D] array — `expected_reliability`,
  * ipynb beta :260-267.  pred is [T][n_values] float64 on the device; out is [T] float64. */
 int svoc_expected_reliability(const double *pred, int64_t n_arrays, int32_t n_values, double *out,

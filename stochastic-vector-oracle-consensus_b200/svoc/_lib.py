@@ -64,6 +64,7 @@ SYMBOLS = {
     "svoc_consensus_float": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs), C.c_void_p]),
     "svoc_consensus_fixed_host": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
     "svoc_consensus_float_host": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
+    "svoc_consensus_float_host_noalloc": (C.c_int, [C.POINTER(SvocConfig), C.c_void_p, C.c_int64, C.POINTER(SvocOutputs)]),
     "svoc_expected_reliability": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "svoc_rank_array": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "svoc_generate": (C.c_int, [C.POINTER(SvocGenConfig), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
