@@ -199,7 +199,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
             }
             __syncwarp(w.cmask);
             // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
-            int b1 = -1, b2 = -1, b3 = -1;
+            int b1 = -1, b2 = -1;
             for (int base = w.part; base < m; base += 4 * WP) {
                 const int a0 = base, a1 = base + WP, a2 = base + 2 * WP, a3 = base + 3 * WP;
                 const in_t v0 = lc[a0 * WD];
@@ -217,7 +217,6 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
                     const int code = (rk << 8) | slot;
                     if (rk <= j1 && code > b1) b1 = code;
                     if (rk <= j2 && code > b2) b2 = code;
-                    if (code > b3) b3 = code;
                 };
                 note(r0, a0);
                 if (a1 < m) note(r1, a1);
@@ -227,11 +226,10 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
             auto imax = [](int a, int b) { return a > b ? a : b; };
             b1 = col_reduce(w, b1, imax);
             b2 = col_reduce(w, b2, imax);
-            b3 = col_reduce(w, b3, imax);
             v_lo = lc[(b1 & 0xff) * WD];
             v_hi = lc[(b2 & 0xff) * WD];
-            thr = lc[(b3 & 0xff) * WD];
-            rescue = j2 >= m;
+            rescue = j2 >= m;             // rank khi above the window: every rank is <= j2 then, so v_hi is the
+            thr = v_hi;                   // window's largest value, the threshold of the rescue scan
             __syncwarp(w.cmask);                  // the list may be overwritten by the next selection
         } else {
             // crowded window (rare): its value range decides between "all one value" and a finer re-keying
@@ -504,11 +502,19 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
             hi = std::numeric_limits<in_t>::lowest();
             const int ns = min(64 / P, max(0, min(N, row_lo + RP) - row_lo));
             const in_t *ptr = tile + row_lo * D + w.c;
-#pragma unroll 16
-            for (int k = 0; k < ns; ++k, ptr += D) {
-                const in_t x = *ptr;
-                lo = vmin(lo, x);
-                hi = vmax(hi, x);
+            if (ns == 16) {                      // the usual case, fully unrolled: sixteen loads at constant offsets
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const in_t x = ptr[k * D];
+                    lo = vmin(lo, x);
+                    hi = vmax(hi, x);
+                }
+            } else {
+                for (int k = 0; k < ns; ++k, ptr += D) {
+                    const in_t x = *ptr;
+                    lo = vmin(lo, x);
+                    hi = vmax(hi, x);
+                }
             }
             lo = col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
             hi = col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
@@ -641,6 +647,26 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
                     }
                 }
                 if (lane == 0) *sel_s = fast ? 1 : 0;
+            } else if (warp == 1) {
+                // meanwhile an idle warp does the first-pass reliability, which needs all risks but no selection
+                acc_t s1 = 0;
+#pragma unroll
+                for (int j = 0; j < NS; ++j)
+                    if (j * 32 + lane < N) s1 += qr_s[j * 32 + lane];
+                for (int o = 16; o; o >>= 1) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                if (lane == 0) {
+                    int stw = STW_OK;
+                    if constexpr (Tr::fixed) {
+                        const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
+                        if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
+                        reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
+                    } else {
+                        const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
+                        if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
+                        reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
+                    }
+                    if (stw != STW_OK) atomicMin(stw_s, stw);
+                }
             }
             __syncthreads();
             if (!*sel_s) {
@@ -706,46 +732,32 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
                 }
                 __syncthreads();
             }
-            // ---- the round's scalars: warp 0, while the others start on their columns
+            // ---- the second-pass reliability and the status: warp 0, while the others start on their columns
             if (warp == 0) {
                 // risks and mask words are read back from shared memory: nothing stays live across the barrier
-                acc_t s1 = 0, s2 = 0;
+                acc_t s2 = 0;
 #pragma unroll
-                for (int j = 0; j < NS; ++j) {
-                    if (j * 32 + lane < N) {
-                        const acc_t qv = qr_s[j * 32 + lane];
-                        s1 += qv;
-                        if ((maskw[j] >> lane) & 1u) s2 += qv;
-                    }
-                }
+                for (int j = 0; j < NS; ++j)
+                    if (j * 32 + lane < N && ((maskw[j] >> lane) & 1u)) s2 += qr_s[j * 32 + lane];
                 if (p.reliable && lane < p.words) p.reliable[(size_t)r * p.words + lane] = maskw[lane];
-                for (int o = 16; o; o >>= 1) {
-                    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-                    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-                }
+                for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
                 if (lane == 0) {
                     int stw = STW_OK;
                     if constexpr (Tr::fixed) {
-                        const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
-                        if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
                         i64 rel2 = 0;
                         if (shape2) stw = min(stw, STW_SECOND_SHAPE);
                         else {
                             rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
                             if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
                         }
-                        reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
                         reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
                     } else {
-                        const val_t rel1 = reliability_float<val_t>(s1 / (val_t)N, p);
-                        if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
                         val_t rel2 = 0;
                         if (shape2) stw = min(stw, STW_SECOND_SHAPE);
                         else {
                             rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
                             if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
                         }
-                        reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
                         reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
                     }
                     if (stw != STW_OK) atomicMin(stw_s, stw);
