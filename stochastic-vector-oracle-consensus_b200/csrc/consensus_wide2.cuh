@@ -86,6 +86,15 @@ __device__ __forceinline__ void w2_build_keys(const W2Ctx &w, const typename Tr:
     }
 }
 
+// r += (u < v) as a compare and a predicated add (the compiler's own choice is an add and a predicated move
+// on top of the compare)
+__device__ __forceinline__ void count_lt(int &r, float u, float v) {
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(r) : "f"(u), "f"(v));
+}
+__device__ __forceinline__ void count_lt(int &r, int32_t u, int32_t v) {
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.s32 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(r) : "r"(u), "r"(v));
+}
+
 // Centre of the flagged rows of this thread's column (all rows when keep == nullptr).  Executed by the P
 // lanes of the column together (shuffles under w.cmask); every one of them returns the result.
 template <class Tr, int DT, int PT, int RPT>
@@ -208,10 +217,10 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
 #pragma unroll 2
                 for (int b = 0; b < m; ++b) {
                     const in_t u = lc[b * WD];
-                    r0 += u < v0 ? 1 : 0;
-                    r1 += u < v1 ? 1 : 0;
-                    r2 += u < v2 ? 1 : 0;
-                    r3 += u < v3 ? 1 : 0;
+                    count_lt(r0, u, v0);
+                    count_lt(r1, u, v1);
+                    count_lt(r2, u, v2);
+                    count_lt(r3, u, v3);
                 }
                 auto note = [&](int rk, int slot) {
                     const int code = (rk << 8) | slot;
