@@ -214,7 +214,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
                 const in_t v0 = lc[a0 * WD];
                 const in_t v1 = a1 < m ? lc[a1 * WD] : v0, v2 = a2 < m ? lc[a2 * WD] : v0, v3 = a3 < m ? lc[a3 * WD] : v0;
                 int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-#pragma unroll 2
+#pragma unroll 1
                 for (int b = 0; b < m; ++b) {
                     const in_t u = lc[b * WD];
                     count_lt(r0, u, v0);
