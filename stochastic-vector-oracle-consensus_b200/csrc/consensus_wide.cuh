@@ -102,24 +102,22 @@ __device__ __forceinline__ int key_byte_sum(const uint8_t *keys, int rp_rt) {
 template <int RPT>
 __device__ __forceinline__ unsigned count_ge(const uint8_t *keys, int rp_rt, unsigned cand, int sum_keys) {
     const int rp = RPT ? RPT : rp_rt;
-    // the pivot constant is split in two opaque halves so that every add is a three-input IADD3 (integer
-    // ALU pipe): the IDP.4A next to it lives on the FMA pipe, which a two-input IMAD.IADD would share
+    // The add is written as VIADDMNMX (max(a + b, 0) on unsigned words is a + b): that instruction lives on the
+    // integer ALU pipe, while the plain add is compiled to IMAD.IADD on the FMA pipe, which IDP.4A already fills.
     const unsigned cb = (128u - cand) * 0x01010101u;
-    unsigned ca = cb >> 1, cc = cb - (cb >> 1);
-    asm volatile("" : "+r"(ca), "+r"(cc));
     int acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
 #pragma unroll
     for (int g = 0; g < rp; g += 32) {
         const uint4 a = *reinterpret_cast<const uint4 *>(keys + g);
         const uint4 b = *reinterpret_cast<const uint4 *>(keys + g + 16);
-        acc0 = __dp4a((int)(a.x + ca + cc), 0x01010101, acc0);
-        acc1 = __dp4a((int)(a.y + ca + cc), 0x01010101, acc1);
-        acc2 = __dp4a((int)(a.z + ca + cc), 0x01010101, acc2);
-        acc3 = __dp4a((int)(a.w + ca + cc), 0x01010101, acc3);
-        acc0 = __dp4a((int)(b.x + ca + cc), 0x01010101, acc0);
-        acc1 = __dp4a((int)(b.y + ca + cc), 0x01010101, acc1);
-        acc2 = __dp4a((int)(b.z + ca + cc), 0x01010101, acc2);
-        acc3 = __dp4a((int)(b.w + ca + cc), 0x01010101, acc3);
+        acc0 = __dp4a((int)__viaddmax_u32(a.x, cb, 0u), 0x01010101, acc0);
+        acc1 = __dp4a((int)__viaddmax_u32(a.y, cb, 0u), 0x01010101, acc1);
+        acc2 = __dp4a((int)__viaddmax_u32(a.z, cb, 0u), 0x01010101, acc2);
+        acc3 = __dp4a((int)__viaddmax_u32(a.w, cb, 0u), 0x01010101, acc3);
+        acc0 = __dp4a((int)__viaddmax_u32(b.x, cb, 0u), 0x01010101, acc0);
+        acc1 = __dp4a((int)__viaddmax_u32(b.y, cb, 0u), 0x01010101, acc1);
+        acc2 = __dp4a((int)__viaddmax_u32(b.z, cb, 0u), 0x01010101, acc2);
+        acc3 = __dp4a((int)__viaddmax_u32(b.w, cb, 0u), 0x01010101, acc3);
     }
     return (unsigned)(sum_keys + rp * (int)(128u - cand) - ((acc0 + acc1) + (acc2 + acc3))) >> 8;
 }
