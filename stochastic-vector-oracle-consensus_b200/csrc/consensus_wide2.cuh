@@ -30,6 +30,12 @@ constexpr int W2_THREADS = W2_THREADS_N;
 constexpr int W2_CTAS_PER_SM = 1024 / W2_THREADS;
 constexpr int W2_CAP = 32;
 constexpr int W2_RCAP = 32;          // rows of the cut bucket one warp ranks exactly (one per lane)
+#ifndef W2_CHUNK
+#define W2_CHUNK 2
+#endif
+#ifndef W2_RANKW
+#define W2_RANKW 4
+#endif
 #ifndef W2_SELECT_FAST
 #define W2_SELECT_FAST 1
 #endif
@@ -184,53 +190,55 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
         in_t thr = const_value;
         uint32_t kmin = 0xffffffffu, kmax = 0u;
         if (m <= W2_CAP) {
-            // values of this part's window rows -> slots off..  Four loads are issued before the first value is
-            // stored: one L2 round trip per four rows instead of one per row
+            // values of this part's window rows -> slots off..  W2_CHUNK loads are issued before the first value is
+            // stored (W2_CHUNK = 2 measured best: 1 serialises the round trips, 4 spends too many idle slots)
             int k = off;
 #pragma unroll
             for (int g = 0; g < (RPT ? RPT : 512); g += 32) {
                 unsigned acc = fl[g / 32];
                 while (acc) {
-                    in_t v[4];
-                    bool on[4];
+                    in_t v[W2_CHUNK];
+                    bool on[W2_CHUNK];
                     const int pos0 = __ffs(acc) - 1;
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
+                    for (int u = 0; u < W2_CHUNK; ++u) {
                         on[u] = acc != 0u;
                         const int pos = on[u] ? __ffs(acc) - 1 : pos0;   // idle slots re-read a valid row
                         acc &= acc - 1;
                         v[u] = tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c];
                     }
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
+                    for (int u = 0; u < W2_CHUNK; ++u)
                         if (on[u]) lc[(k++) * WD] = v[u];
                 }
             }
             __syncwarp(w.cmask);
             // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
             int b1 = -1, b2 = -1;
-            for (int base = w.part; base < m; base += 4 * WP) {
-                const int a0 = base, a1 = base + WP, a2 = base + 2 * WP, a3 = base + 3 * WP;
-                const in_t v0 = lc[a0 * WD];
-                const in_t v1 = a1 < m ? lc[a1 * WD] : v0, v2 = a2 < m ? lc[a2 * WD] : v0, v3 = a3 < m ? lc[a3 * WD] : v0;
-                int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+            for (int base = w.part; base < m; base += W2_RANKW * WP) {
+                in_t v[W2_RANKW];
+                int rr[W2_RANKW];
+#pragma unroll
+                for (int t = 0; t < W2_RANKW; ++t) {
+                    const int a = base + t * WP;
+                    v[t] = a < m ? lc[a * WD] : lc[base * WD];
+                    rr[t] = 0;
+                }
 #pragma unroll 1
                 for (int b = 0; b < m; ++b) {
                     const in_t u = lc[b * WD];
-                    count_lt(r0, u, v0);
-                    count_lt(r1, u, v1);
-                    count_lt(r2, u, v2);
-                    count_lt(r3, u, v3);
+#pragma unroll
+                    for (int t = 0; t < W2_RANKW; ++t) count_lt(rr[t], u, v[t]);
                 }
-                auto note = [&](int rk, int slot) {
-                    const int code = (rk << 8) | slot;
-                    if (rk <= j1 && code > b1) b1 = code;
-                    if (rk <= j2 && code > b2) b2 = code;
-                };
-                note(r0, a0);
-                if (a1 < m) note(r1, a1);
-                if (a2 < m) note(r2, a2);
-                if (a3 < m) note(r3, a3);
+#pragma unroll
+                for (int t = 0; t < W2_RANKW; ++t) {
+                    const int a = base + t * WP;
+                    if (a < m) {                      // largest (rank, slot) code with rank <= j1 / j2
+                        const int code = (rr[t] << 8) | a;
+                        if (rr[t] <= j1 && code > b1) b1 = code;
+                        if (rr[t] <= j2 && code > b2) b2 = code;
+                    }
+                }
             }
             auto imax = [](int a, int b) { return a > b ? a : b; };
             b1 = col_reduce(w, b1, imax);
@@ -547,6 +555,11 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
             }
         }
         __syncthreads();
+        // the first sweep of this round is done: pull the CTA's next round towards L2 now (two rounds per CTA, 76 MB
+        // in all, fit the L2; issued at the start of the round it evicted lines still in use, issued after the
+        // risk sweep it came 0.5 % too late)
+        if (tid == 0 && r + gridDim.x < p.T)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(tile + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
 
         // ---- phase 2: quadratic risk of every row.  A warp reads one whole row per request (lane <-> 4
         //      consecutive dimensions, 512 contiguous bytes for D = 128), so the loads are fully coalesced;
@@ -622,10 +635,6 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
             }
         }
         __syncthreads();
-        // the last full sweep of this round is done: pull the next round towards L2 now, so that it is resident
-        // only while it is about to be used
-        if (tid == 0 && r + gridDim.x < p.T)
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(tile + (size_t)gridDim.x * round_elems), "r"(round_bytes) : "memory");
 
         // ---- phase 3: which rows are kept.  Warp 0 works it out alone (w2_select_rows) while the others wait;
         //      the all-pairs ranking — rank of every row under (qr asc, index desc | asc), rows spread over all
