@@ -92,11 +92,14 @@ class ClockSampler:
                 with self._lock:
                     self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
-    def wait_first(self, timeout=10.0):
+    def wait_first(self, timeout=10.0, samples=2):
+        """Block until the sampler has settled: `samples` lines have arrived.  The start-up of nvidia-smi reaches
+        past its first line — a timed step that began right after the first sample was stretched by 100-400 ms
+        in one run out of three, always the second step; after the second sample none was (tools/hiccup_probe.py)."""
         end = time.time() + timeout
         while self.proc is not None and time.time() < end:
             with self._lock:
-                if self.rows:
+                if len(self.rows) >= samples:
                     return
             time.sleep(0.02)
 

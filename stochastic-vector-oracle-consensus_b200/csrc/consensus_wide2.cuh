@@ -28,7 +28,13 @@ namespace svoc {
 #endif
 constexpr int W2_THREADS = W2_THREADS_N;
 constexpr int W2_CTAS_PER_SM = 1024 / W2_THREADS;
-constexpr int W2_CAP = 32;
+#ifndef W2_CAP_N
+#define W2_CAP_N 32
+#endif
+#ifndef W2_SAMPLE
+#define W2_SAMPLE 64
+#endif
+constexpr int W2_CAP = W2_CAP_N;
 constexpr int W2_RCAP = 32;          // rows of the cut bucket one warp ranks exactly (one per lane)
 #ifndef W2_CHUNK
 #define W2_CHUNK 2
@@ -517,11 +523,11 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
             // key scale from a sample: the first 64/P rows of every part (values outside clamp to the end buckets)
             lo = std::numeric_limits<in_t>::max();
             hi = std::numeric_limits<in_t>::lowest();
-            const int ns = min(64 / P, max(0, min(N, row_lo + RP) - row_lo));
+            const int ns = min(W2_SAMPLE / P, max(0, min(N, row_lo + RP) - row_lo));
             const in_t *ptr = tile + row_lo * D + w.c;
-            if (ns == 16) {                      // the usual case, fully unrolled: sixteen loads at constant offsets
+            if (ns == W2_SAMPLE / 4) {           // the usual case, fully unrolled: loads at constant offsets
 #pragma unroll
-                for (int k = 0; k < 16; ++k) {
+                for (int k = 0; k < W2_SAMPLE / 4; ++k) {
                     const in_t x = ptr[k * D];
                     lo = vmin(lo, x);
                     hi = vmax(hi, x);
