@@ -19,6 +19,7 @@ cannot run on the box), with all host threads, and prints the same line with imp
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -58,14 +59,13 @@ def measured_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 250:
-    about one query in sixty stalls the running kernel for 30-100 ms on these boxes — measured with
-    tools/hiccup.sh, 0 slow steps in 80 without the sampler — so the period is kept as long as a short timed
-    region allows).
-    The process is started BEFORE the warm-up steps and the timed region only begins once its first sample has
-    arrived: nvidia-smi's start-up (NVML initialisation) can stall a running kernel for ~100 ms, which must not
-    land inside the timed steps.  `with sampler:` brackets the timed region; only samples that arrived inside
-    it are summarised."""
+    """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 250).
+    The process is started BEFORE the warm-up steps and the timed region only begins once two samples have
+    arrived, so that its start-up does not overlap the timed steps.  `with sampler:` brackets the timed region;
+    only samples that arrived inside it are summarised.  (A step stretched two- to threefold in one run out of
+    five, always the second timed step, was first blamed on this sampler; tools/hiccup_probe.py showed the
+    queries do not disturb the kernels, and the stretch disappeared when the Python garbage collector was
+    paused for the timed region — see main().)"""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
@@ -93,9 +93,7 @@ class ClockSampler:
                     self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
 
     def wait_first(self, timeout=10.0, samples=2):
-        """Block until the sampler has settled: `samples` lines have arrived.  The start-up of nvidia-smi reaches
-        past its first line — a timed step that began right after the first sample was stretched by 100-400 ms
-        in one run out of three, always the second step; after the second sample none was (tools/hiccup_probe.py)."""
+        """Block until `samples` lines have arrived (the sampler's start-up is then over)."""
         end = time.time() + timeout
         while self.proc is not None and time.time() < end:
             with self._lock:
@@ -270,12 +268,15 @@ def fused_arm(args, wl, torch, svoc, dist, dev, rank, world, local):
     barrier()
     l0 = svoc.launch_count()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    gc.collect()
+    gc.disable()
     with clk:
         a.record()
         for _ in range(args.steps):
             st = step()
         b.record()
         barrier()
+    gc.enable()
     t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -375,7 +376,9 @@ def main():
     l0 = svoc.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 2)]
     kern_ms = []
-    with clk:
+    gc.collect()
+    gc.disable()       # a generation-2 collection (~50-150 ms of host time) landed in the second timed step of one
+    with clk:          # run in five: the device then waits for its next launch and the step looks stretched
         ev[0].record()
         for i in range(args.steps):
             ev[2 * i + 1].record()
@@ -386,6 +389,7 @@ def main():
                 stats.allreduce()
         ev[-1].record()
         barrier()
+    gc.enable()
     total_ms = ev[0].elapsed_time(ev[-1])
     kern_ms = [ev[2 * i + 1].elapsed_time(ev[2 * i + 2]) for i in range(args.steps)]
     launches = svoc.launch_count() - l0
