@@ -62,10 +62,8 @@ class ClockSampler:
     """nvidia-smi clocks / throttle reasons while the timed region runs (one nvidia-smi process, -lms 250).
     The process is started BEFORE the warm-up steps and the timed region only begins once two samples have
     arrived, so that its start-up does not overlap the timed steps.  `with sampler:` brackets the timed region;
-    only samples that arrived inside it are summarised.  (A step stretched two- to threefold in one run out of
-    five, always the second timed step, was first blamed on this sampler; tools/hiccup_probe.py showed the
-    queries do not disturb the kernels, and the stretch disappeared when the Python garbage collector was
-    paused for the timed region — see main().)"""
+    only samples that arrived inside it are summarised.  (tools/hiccup_probe.py: the queries themselves do not
+    disturb running kernels.)"""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
@@ -370,15 +368,20 @@ def main():
         return r
 
     clk = ClockSampler(local).start()      # started before the warm-up, see the class comment
+    # The warm-up keeps the previous step's result alive while the next step allocates its outputs, exactly as the
+    # timed loop below does: torch's caching allocator then holds both output sets before the timed region.
+    # (Without this the second timed step paid for a fresh cudaMalloc of ~0.6 GB of outputs — a step stretched
+    # by 40-160 ms in one run out of five.)
+    r = None
     for _ in range(max(3, args.warmup)):
-        step()
+        r = step()
     barrier()
     l0 = svoc.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 2)]
     kern_ms = []
     gc.collect()
-    gc.disable()       # a generation-2 collection (~50-150 ms of host time) landed in the second timed step of one
-    with clk:          # run in five: the device then waits for its next launch and the step looks stretched
+    gc.disable()       # no collector pause on the host while the device waits for its next launch
+    with clk:
         ev[0].record()
         for i in range(args.steps):
             ev[2 * i + 1].record()

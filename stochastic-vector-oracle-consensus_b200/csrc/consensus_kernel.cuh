@@ -444,8 +444,15 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
 }
 
 // ------------------------------------------------------------------------------ the kernel
+// Resident CTAs per SM the compiler must make room for: three for the 64-row networks (168 registers), eight for
+// the fp32 32-row kernel (64 registers instead of 113: +20 % on the config-5 shape — latency hiding beats the
+// few extra moves), no constraint elsewhere (64-bit arithmetic spills under a tight register cap).
 template <class Tr, int NPAD>
-__global__ void __launch_bounds__(NPAD == 0 ? 256 : 128, NPAD == 64 ? 3 : 1) consensus_kernel(const Params p) {
+constexpr int small_min_ctas() {
+    return NPAD == 64 ? 3 : ((NPAD == 32 && !Tr::fixed && sizeof(typename Tr::acc_t) == 4) ? 8 : 1);
+}
+template <class Tr, int NPAD>
+__global__ void __launch_bounds__(NPAD == 0 ? 256 : 128, small_min_ctas<Tr, NPAD>()) consensus_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;

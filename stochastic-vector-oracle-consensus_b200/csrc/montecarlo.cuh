@@ -22,7 +22,8 @@ struct McParams {
 };
 
 template <class Tr, int NPAD>
-__global__ void __launch_bounds__(NPAD == 0 ? 256 : 128) montecarlo_kernel(const Params p, const McParams m) {
+__global__ void __launch_bounds__(NPAD == 0 ? 256 : 128, (NPAD > 0 && NPAD <= 32 && !Tr::fixed && sizeof(typename Tr::acc_t) == 4) ? 8 : 1)
+montecarlo_kernel(const Params p, const McParams m) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
