@@ -444,12 +444,13 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
 }
 
 // ------------------------------------------------------------------------------ the kernel
-// Resident CTAs per SM the compiler must make room for: three for the 64-row networks (168 registers), eight for
+// Resident CTAs per SM the compiler must make room for: three for the 64-row networks (168 registers; four, 128
+// registers with some spills, for int32 fixed point: +7 % on config 3), eight for
 // the fp32 32-row kernel (64 registers instead of 113: +20 % on the config-5 shape — latency hiding beats the
 // few extra moves), no constraint elsewhere (64-bit arithmetic spills under a tight register cap).
 template <class Tr, int NPAD>
 constexpr int small_min_ctas() {
-    return NPAD == 64 ? 3 : ((NPAD == 32 && !Tr::fixed && sizeof(typename Tr::acc_t) == 4) ? 8 : 1);
+    return NPAD == 64 ? ((Tr::fixed && sizeof(typename Tr::in_t) == 4) ? 4 : 3) : ((NPAD == 32 && !Tr::fixed && sizeof(typename Tr::acc_t) == 4) ? 8 : 1);
 }
 template <class Tr, int NPAD>
 __global__ void __launch_bounds__(NPAD == 0 ? 256 : 128, small_min_ctas<Tr, NPAD>()) consensus_kernel(const Params p) {
