@@ -15,7 +15,8 @@
  *   - return value 0 = ok, negative = bad argument / CUDA error (text via
  *     svoc_last_error()); per-round data errors (the contract's panics) go to
  *     status[T], never to the return code;
- *   - no CPU fallback exists: without a CUDA device every compute call fails.
+ *   - no CPU fallback exists: without a CUDA device every compute call fails;
+ *   - float form: inputs must be finite (NaN / inf are not detected; the results of such a round are unspecified).
  */
 #ifndef SVOC_H
 #define SVOC_H
@@ -50,7 +51,8 @@ extern "C" {
 #define SVOC_ST_SQRT_REL1 2         /* math.cairo:271-292: sqrt(1) divides by zero */
 #define SVOC_ST_MAX_SPREAD_ZERO 3   /* contract.cairo:365-368 */
 #define SVOC_ST_REL1_RANGE 4        /* math.cairo:294-296 after contract.cairo:467 / :397 */
-#define SVOC_ST_SECOND_PASS_SHAPE 5 /* fewer than 2 (constrained) / 1 reliable rows */
+#define SVOC_ST_SECOND_PASS_SHAPE 5 /* too few reliable rows for the second-pass centre: < 2 for the smooth median
+                                       (math.cairo:117 reads sorted[mid-1]), < 1 for np.median / the mean */
 #define SVOC_ST_SQRT_REL2 6
 #define SVOC_ST_REL2_RANGE 7        /* contract.cairo:488 / :419 */
 #define SVOC_ST_SKEW_PANIC 8        /* math.cairo:320-338: variance in {0,1} or R <= 2 */
@@ -114,7 +116,9 @@ int svoc_consensus_float(const svoc_config *cfg, const void *pred, int64_t n_rou
 /* Same two calls with HOST buffers: predictions are staged to the device in chunks on
  * internal streams and the outputs copied back; the call returns when the outputs are
  * complete.  This is the call a client holding numpy arrays makes
- * (client/contract.py:200-208 `update_all_the_predictions` is its on-chain analogue). */
+ * (client/contract.py:200-208 `update_all_the_predictions` is its on-chain analogue).
+ * out->skew / out->kurt are written only when cfg->want_moments is set (left untouched otherwise).  When an
+ * error is returned no copy from or into the caller's buffers is still in flight. */
 int svoc_consensus_fixed_host(const svoc_config *cfg, const void *pred, int64_t n_rounds,
                               const svoc_outputs *out);
 int svoc_consensus_float_host(const svoc_config *cfg, const void *pred, int64_t n_rounds,
@@ -223,7 +227,8 @@ const char *svoc_last_error(void);
 int svoc_version(void);
 /* number of kernels this library has launched in the calling process (for bench.py's gpu_launches) */
 int64_t svoc_launch_count(void);
-/* name of the kernel variant the dispatcher picks for (cfg): "small<NPAD>" or "generic" */
+/* name of the kernel variant the dispatcher picks for (cfg), for diagnostics and bench labels: "small8" .. "small64"
+ * (N <= 64), "wide3" / "wide2" / "wide" (64 < N <= 512, 32-bit elements) or "generic" */
 const char *svoc_kernel_variant(const svoc_config *cfg);
 
 #ifdef __cplusplus

@@ -16,21 +16,43 @@ _SO = os.path.join(_HERE, "libsvoc_ref.so")
 _lib = None
 
 
+def _cpu_stamp() -> str:
+    """Identifies the host CPU: the library is built with -march=native, so one built on another machine
+    (it travels with the tree) must be rebuilt before it is loaded."""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    flags = next((l for l in f if l.startswith("flags")), "")
+                    import zlib
+                    return f"{line.split(':', 1)[1].strip()} / {zlib.crc32(flags.encode()):08x}"
+    except OSError:
+        pass
+    return "unknown"
+
+
 def build(force: bool = False) -> str:
     src = os.path.join(_HERE, "svoc_ref.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    stamp_file = _SO + ".cpu"
+    stamp = _cpu_stamp()
+    try:
+        same_cpu = open(stamp_file).read() == stamp
+    except OSError:
+        same_cpu = False
+    if force or not same_cpu or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
         env = dict(os.environ)
         env["CC"] = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
         subprocess.check_call(["make", "-B", "-C", _HERE, "libsvoc_ref.so"], env=env,
                               stdout=subprocess.DEVNULL)
+        with open(stamp_file, "w") as f:
+            f.write(stamp)
     return _SO
 
 
 def lib():
     global _lib
     if _lib is None:
-        if not os.path.exists(_SO):
-            build()
+        build()
         _lib = C.CDLL(_SO)
         _lib.svoc_ref_max_threads.restype = C.c_int
     return _lib

@@ -16,7 +16,7 @@
  * Float form: the same evaluation order in double precision, plus the
  * notebook's true-median / lower-index-kept variant (ipynb beta :342-371).
  *
- * Build: see oracle/Makefile  (gcc -O2 -shared -fPIC -pthread); threads are plain pthreads.
+ * Build: see oracle/Makefile  (gcc -O2 -march=native -shared -fPIC -pthread); threads are plain pthreads.
  */
 #include <stdint.h>
 #include <stdlib.h>
@@ -63,21 +63,41 @@ static i128 wsqrt(ctx_t *c, i128 v) {
 }
 
 /* ---- selection helpers (int64 values) */
-static int cmp_i64(const void *a, const void *b) { int64_t x = *(const int64_t *)a, y = *(const int64_t *)b; return (x > y) - (x < y); }
-static void sort_i64(int64_t *a, int n) {           /* any correct ascending sort gives the same multiset order */
-    if (n > 48) { qsort(a, (size_t)n, sizeof(int64_t), cmp_i64); return; }
-    for (int i = 1; i < n; ++i) {
-        int64_t v = a[i]; int j = i;
-        while (j >= 1 && a[j - 1] > v) { a[j] = a[j - 1]; --j; }
-        a[j] = v;
+/* Only the two middle order statistics of a column are used (math.cairo:113-126 reads sorted[mid-1] and
+ * sorted[mid] of alexandria's MergeSort output), and they depend on the multiset alone, so a selection gives
+ * the same numbers as the full sort: quickselect (median-of-three pivot, Hoare partition) puts the mid-th
+ * smallest at a[mid] with everything left of it <= a[mid]; sorted[mid-1] is then the maximum of the left part. */
+#define SELECT_BODY(T)                                                                   \
+    int lo = 0, hi = n - 1;                                                              \
+    while (hi - lo > 16) {                                                               \
+        int m = lo + (hi - lo) / 2;                                                      \
+        T t;                                                                             \
+        if (a[m] < a[lo]) { t = a[m]; a[m] = a[lo]; a[lo] = t; }                         \
+        if (a[hi] < a[lo]) { t = a[hi]; a[hi] = a[lo]; a[lo] = t; }                      \
+        if (a[hi] < a[m]) { t = a[hi]; a[hi] = a[m]; a[m] = t; }                         \
+        T pv = a[m];                                                                     \
+        int i = lo, j = hi;                                                              \
+        while (i <= j) {                                                                 \
+            while (a[i] < pv) ++i;                                                       \
+            while (pv < a[j]) --j;                                                       \
+            if (i <= j) { t = a[i]; a[i] = a[j]; a[j] = t; ++i; --j; }                   \
+        }                                                                                \
+        if (k <= j) hi = j; else if (k >= i) lo = i; else return;                        \
+    }                                                                                    \
+    for (int i = lo + 1; i <= hi; ++i) {                                                 \
+        T v = a[i]; int j = i;                                                           \
+        while (j > lo && a[j - 1] > v) { a[j] = a[j - 1]; --j; }                         \
+        a[j] = v;                                                                        \
     }
-}
+static void select_i64(int64_t *a, int n, int k) { SELECT_BODY(int64_t) }
 
 /* math.cairo:113-126: (s[mid-1] + s[mid]) / 2, mid = n/2; the 3-value branch is dead. */
 static i128 smooth_median_i64(ctx_t *c, int64_t *tmp, int n) {
-    sort_i64(tmp, n);
     int mid = n / 2;
-    return tdiv(c, add_c(c, tmp[mid - 1], tmp[mid]), 2);
+    select_i64(tmp, n, mid);
+    int64_t below = tmp[0];
+    for (int i = 1; i < mid; ++i) if (tmp[i] > below) below = tmp[i];
+    return tdiv(c, add_c(c, below, tmp[mid]), 2);
 }
 
 static i128 reliability_fixed(ctx_t *c, i128 avg_qr, int dim, int constrained, i128 max_spread, int st_sqrt) {
@@ -246,14 +266,16 @@ int svoc_ref_fixed(const int64_t *pred, long T, int N, int D, int F, int constra
 }
 
 /* ------------------------------------------------------------------ float form (double) */
-static int cmp_d(const void *a, const void *b) { double x = *(const double *)a, y = *(const double *)b; return (x > y) - (x < y); }
+static void select_d(double *a, int n, int k) { SELECT_BODY(double) }
 
 static double centre_d(double *tmp, int n, int kind) {
     if (kind == 2) { double s = 0; for (int i = 0; i < n; ++i) s += tmp[i]; return s / n; }
-    qsort(tmp, (size_t)n, sizeof(double), cmp_d);
     int mid = n / 2;
-    if (kind == 1) return (n & 1) ? tmp[mid] : 0.5 * (tmp[mid - 1] + tmp[mid]);   /* np.median */
-    return 0.5 * (tmp[mid - 1] + tmp[mid]);                                        /* math.cairo:113-126 */
+    select_d(tmp, n, mid);                                                         /* tmp[mid] = sorted[mid] */
+    if (kind == 1 && (n & 1)) return tmp[mid];                                     /* np.median, odd length */
+    double below = tmp[0];                                                         /* sorted[mid-1] */
+    for (int i = 1; i < mid; ++i) if (tmp[i] > below) below = tmp[i];
+    return 0.5 * (below + tmp[mid]);                               /* np.median (even) / math.cairo:113-126 */
 }
 
 static double rel_d(double avg, int D, int constrained, double ms) {

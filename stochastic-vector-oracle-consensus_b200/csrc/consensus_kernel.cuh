@@ -77,6 +77,14 @@ __device__ __forceinline__ void centre_ranks(int kind, int n, int &klo, int &khi
     if (klo < 0) klo = 0;  // n < 2 is reported through the status word
 }
 
+// The second pass panics on its shape when its centre cannot be formed from R rows: the contract's smooth median
+// reads sorted[mid - 1] and sorted[mid] (math.cairo:117: at least two rows), np.median and the mean take one row
+// (ipynb beta :369-371 restricted_median over a single kept oracle is valid).  With the contract's own settings
+// (constrained -> smooth median, unconstrained -> mean) this is "R < 2 constrained, R < 1 unconstrained".
+__device__ __forceinline__ bool second_pass_shape_panic(const Params &p) {
+    return p.centre2 == SVOC_CENTRE_SMOOTH_MEDIAN_CAIRO ? p.R < 2 : p.R < 1;
+}
+
 // ------------------------------------------------------------------------------ moments
 // skewness / kurtosis of one column over the R reliable rows (math.cairo:208-222, 320-363).
 // `fe(f)` calls f(x) for every reliable value.
@@ -383,7 +391,7 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
             if (second) { for (int i = 0; i < N; ++i) if (kp[i]) sum += q[i]; }
             else { for (int i = 0; i < N; ++i) sum += q[i]; }
             int stw = STW_OK;
-            const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+            const bool shape2 = second_pass_shape_panic(p);
             if (!second && N < 2) stw = min(stw, STW_FIRST_SHAPE);
             if (second && shape2) stw = min(stw, STW_SECOND_SHAPE);
             const int cnt = second ? R : N;
@@ -416,7 +424,7 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
     }
 
     // ---- phase 4: second-pass centre over the reliable rows (+ moments)
-    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+    const bool shape2 = second_pass_shape_panic(p);
     for (int c = tid; c < nr * D; c += nt) {
         const int r = c / D, d = c - r * D;
         const in_t *col = tile + (size_t)r * round_elems + d;

@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(NT, GT ? 2 : 1) consensus_wide_kernel(const Pa
     uint32_t parity = 0;
     int buf = 0;
     const int row_lo = w.part * RP, row_hi = min(N, (w.part + 1) * RP);
-    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+    const bool shape2 = second_pass_shape_panic(p);
 
     for (i64 r = blockIdx.x; r < p.T; r += gridDim.x) {
         const in_t *gsrc = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;

@@ -510,7 +510,7 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
     const size_t round_elems = (size_t)N * D;
     const uint32_t round_bytes = (uint32_t)(round_elems * sizeof(in_t));
     const int row_lo = w.part * RP;
-    const bool shape2 = p.constrained ? (R < 2) : (R < 1);
+    const bool shape2 = second_pass_shape_panic(p);
 
     for (i64 r = blockIdx.x; r < p.T; r += gridDim.x) {
         const in_t *tile = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * round_elems;

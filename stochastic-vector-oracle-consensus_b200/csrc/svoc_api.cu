@@ -41,12 +41,15 @@ static size_t smem_bytes(const svoc_config &c, int rb, int tile_smem) {
     return s;
 }
 
+// SM count of the CURRENT device (cached per ordinal: a process may drive different GPUs)
 static int sm_count() {
-    static int n = 0;
+    static int cache[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cache[dev];
     if (n == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev] = n;
     }
     return n;
 }

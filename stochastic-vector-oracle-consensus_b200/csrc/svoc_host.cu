@@ -24,7 +24,9 @@ struct HostWorkspace {
     size_t cap = 0;
 };
 
-std::mutex g_ws_mu;
+// one lock per device: calls on the same device share its staging buffers and streams and are serialised, calls
+// that drive different GPUs run side by side
+std::mutex g_ws_mu[16];
 HostWorkspace g_ws[16];
 
 #define CK(call)                                                                       \
@@ -51,8 +53,9 @@ ChunkLayout layout(const svoc_config &c, const svoc_outputs &o, int64_t rounds, 
     L.reliable = take(o.reliable ? T * W * 4 : 0);
     L.consensus = take(T * D * vs);
     L.rel2 = take(T * vs);
-    L.skew = take(o.skew ? T * D * vs : 0);
-    L.kurt = take(o.kurt ? T * D * vs : 0);
+    // the kernels write skew / kurt only when moments are requested: no staging (and no copy back) otherwise
+    L.skew = take(o.skew && c.want_moments ? T * D * vs : 0);
+    L.kurt = take(o.kurt && c.want_moments ? T * D * vs : 0);
     L.status = take(T * 4);
     L.rank = take(o.rank ? T * N * 4 : 0);
     L.total = off;
@@ -81,7 +84,7 @@ int consensus_host(const svoc_config *cfg, const void *pred, int64_t T, const sv
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 16) return fail("device ordinal out of range");
-    std::lock_guard<std::mutex> lk(g_ws_mu);
+    std::lock_guard<std::mutex> lk(g_ws_mu[dev]);
     HostWorkspace &ws = g_ws[dev];
     if (ws.device != dev) {
         for (int k = 0; k < 2; ++k) CK(cudaStreamCreateWithFlags(&ws.st[k], cudaStreamNonBlocking));
@@ -97,7 +100,12 @@ int consensus_host(const svoc_config *cfg, const void *pred, int64_t T, const sv
         ws.cap = L.total;
     }
 
+    const bool moments = cfg->want_moments != 0;
+    void *const h_skew = moments ? out->skew : nullptr, *const h_kurt = moments ? out->kurt : nullptr;
     const unsigned char *hin = static_cast<const unsigned char *>(pred);
+    // the pipeline proper; on any failure after the first enqueue the caller below drains both streams, so that no
+    // copy into or out of the caller's buffers is still in flight when the error is returned
+    auto pipeline = [&]() -> int {
     int k = 0;
     for (int64_t t0 = 0; t0 < T; t0 += chunk, k ^= 1) {
         const int64_t n = std::min<int64_t>(chunk, T - t0);
@@ -111,8 +119,8 @@ int consensus_host(const svoc_config *cfg, const void *pred, int64_t T, const sv
         d.reliable = out->reliable ? reinterpret_cast<uint32_t *>(b + L.reliable) : nullptr;
         d.consensus = b + L.consensus;
         d.rel2 = b + L.rel2;
-        d.skew = out->skew ? b + L.skew : nullptr;
-        d.kurt = out->kurt ? b + L.kurt : nullptr;
+        d.skew = h_skew ? b + L.skew : nullptr;
+        d.kurt = h_kurt ? b + L.kurt : nullptr;
         d.status = reinterpret_cast<int32_t *>(b + L.status);
         d.rank = out->rank ? reinterpret_cast<int32_t *>(b + L.rank) : nullptr;
         if (int rc = consensus_device(cfg, b + L.in, n, &d, st, fixed)) return rc;
@@ -127,14 +135,21 @@ int consensus_host(const svoc_config *cfg, const void *pred, int64_t T, const sv
         CK(back(out->reliable, L.reliable, W * 4));
         CK(back(out->consensus, L.consensus, D * vs));
         CK(back(out->rel2, L.rel2, vs));
-        CK(back(out->skew, L.skew, D * vs));
-        CK(back(out->kurt, L.kurt, D * vs));
+        CK(back(h_skew, L.skew, D * vs));
+        CK(back(h_kurt, L.kurt, D * vs));
         CK(back(out->status, L.status, 4));
         CK(back(out->rank, L.rank, N * 4));
     }
     CK(cudaStreamSynchronize(ws.st[0]));
     CK(cudaStreamSynchronize(ws.st[1]));
     return 0;
+    };
+    const int rc = pipeline();
+    if (rc != 0) {                       // keep the first error's text; the drain's own result is of no interest
+        cudaStreamSynchronize(ws.st[0]);
+        cudaStreamSynchronize(ws.st[1]);
+    }
+    return rc;
 }
 
 }  // namespace

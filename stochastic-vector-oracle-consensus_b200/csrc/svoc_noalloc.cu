@@ -77,12 +77,16 @@ int float_host_noalloc(const svoc_config *cfg, const void *pred, int64_t T, cons
         return fail("svoc_consensus_float_host_noalloc: consensus, rel1, rel2 and status outputs are required");
 
     const size_t es = cfg->dtype == SVOC_F32 ? 4 : 8;     // element size; results have the same type
+    // skewness / kurtosis are produced only when cfg->want_moments is set: without it the two outputs are neither
+    // staged nor copied back (the caller's buffers stay untouched), so nothing the kernels did not write in THIS call
+    // can ever reach the caller
+    void *const h_skew = cfg->want_moments ? out->skew : nullptr, *const h_kurt = cfg->want_moments ? out->kurt : nullptr;
     const size_t N = cfg->n_oracles, D = cfg->dimension, W = (N + 31) / 32, n = (size_t)T;
 
     // carve the staging buffer: predictions first, then one area per requested output
     const size_t cap = (size_t)SVOC_NOALLOC_SCRATCH_BYTES;
     const size_t per_round = N * D * es + (out->essence1 ? D * es : 0) + (out->qr ? N * es : 0) + es + (out->reliable ? W * 4 : 0) +
-                             D * es + es + (out->skew ? D * es : 0) + (out->kurt ? D * es : 0) + 4 + (out->rank ? N * 4 : 0);
+                             D * es + es + (h_skew ? D * es : 0) + (h_kurt ? D * es : 0) + 4 + (out->rank ? N * 4 : 0);
     const size_t fit = cap > 11 * 256 ? (cap - 11 * 256) / per_round : 0;      // every area is padded to 256 bytes
     size_t off = 0;
     auto take = [&](bool wanted, size_t bytes) { const size_t at = off; if (wanted) off += up256(bytes); return at; };
@@ -96,8 +100,8 @@ int float_host_noalloc(const svoc_config *cfg, const void *pred, int64_t T, cons
         a_rl = take(out->reliable != nullptr, n * W * 4);
         a_co = take(true, n * D * es);
         a_r2 = take(true, n * es);
-        a_sk = take(out->skew != nullptr, n * D * es);
-        a_ku = take(out->kurt != nullptr, n * D * es);
+        a_sk = take(h_skew != nullptr, n * D * es);
+        a_ku = take(h_kurt != nullptr, n * D * es);
         a_st = take(true, n * 4);
         a_rk = take(out->rank != nullptr, n * N * 4);
     }
@@ -112,6 +116,9 @@ int float_host_noalloc(const svoc_config *cfg, const void *pred, int64_t T, cons
 
     // everything on the legacy default stream: no stream is created either
     cudaStream_t st = nullptr;
+    // once the first copy is queued an error must not return while work is still in flight: the caller may free
+    // its (pinned) buffers on failure, and the next call would overlap this one in the shared array
+    auto queued = [&]() -> int {
     NA_CK(cudaMemcpyAsync(b + a_in, pred, n * N * D * es, cudaMemcpyHostToDevice, st));
     svoc_outputs d{};
     d.essence1 = out->essence1 ? b + a_e1 : nullptr;
@@ -120,8 +127,8 @@ int float_host_noalloc(const svoc_config *cfg, const void *pred, int64_t T, cons
     d.reliable = out->reliable ? reinterpret_cast<uint32_t *>(b + a_rl) : nullptr;
     d.consensus = b + a_co;
     d.rel2 = b + a_r2;
-    d.skew = out->skew ? b + a_sk : nullptr;
-    d.kurt = out->kurt ? b + a_ku : nullptr;
+    d.skew = h_skew ? b + a_sk : nullptr;
+    d.kurt = h_kurt ? b + a_ku : nullptr;
     d.status = reinterpret_cast<int32_t *>(b + a_st);
     d.rank = out->rank ? reinterpret_cast<int32_t *>(b + a_rk) : nullptr;
     if (int rc = consensus_device(cfg, b + a_in, T, &d, st, false)) return rc;
@@ -134,12 +141,16 @@ int float_host_noalloc(const svoc_config *cfg, const void *pred, int64_t T, cons
     NA_CK(back(out->reliable, a_rl, n * W * 4));
     NA_CK(back(out->consensus, a_co, n * D * es));
     NA_CK(back(out->rel2, a_r2, n * es));
-    NA_CK(back(out->skew, a_sk, n * D * es));
-    NA_CK(back(out->kurt, a_ku, n * D * es));
+    NA_CK(back(h_skew, a_sk, n * D * es));
+    NA_CK(back(h_kurt, a_ku, n * D * es));
     NA_CK(back(out->status, a_st, n * 4));
     NA_CK(back(out->rank, a_rk, n * N * 4));
     NA_CK(cudaStreamSynchronize(st));
     return 0;
+    };
+    const int rc = queued();
+    if (rc != 0) cudaStreamSynchronize(st);      // drain; the first error's text is kept
+    return rc;
 }
 
 }  // namespace

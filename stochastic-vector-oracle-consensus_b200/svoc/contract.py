@@ -48,6 +48,7 @@ class OracleConsensusNDS:
         self.n_failing_oracles = int(n_failing_oracles)
         self.constrained = bool(constrained)
         self.unconstrained_max_spread = felt_to_i128(int(unconstrained_max_spread))
+        self._stray_votes = {}                          # votes written at receiver keys beyond the admin list
         self._reset_votes()
         self.consensus_value = [0] * self.dimension
         self.reliability_first_pass = 0
@@ -160,17 +161,40 @@ class OracleConsensusNDS:
         self.replacement_propositions[a] = (old_index, new_address)
 
     def vote_for_a_proposition(self, which_admin: int, support_his_proposition: bool) -> None:
+        """contract.cairo:718-738.  The vote is written first and the majority check may then panic
+        (`unwrap` of an empty proposition): the transaction reverts, so the written vote is rolled back.
+        `which_admin` beyond the admin list is not an error in the contract — the vote matrix is a storage map,
+        any key can be written and unknown keys read as false — so such votes are kept in a side table."""
         if not self.enable_oracle_replacement:
             raise ContractPanic("replacement disabled")
         voter = self._admin_index()
-        self.vote_matrix[voter][which_admin] = bool(support_his_proposition)
-        self._check_for_replacement(which_admin)
+        which_admin = int(which_admin)
+        if which_admin < 0:
+            raise ContractPanic("usize underflow")
+        in_range = which_admin < len(self.admins)
+        previous = self.vote_matrix[voter][which_admin] if in_range else self._stray_votes.get((voter, which_admin), False)
+        self._write_vote(voter, which_admin, bool(support_his_proposition))
+        try:
+            self._check_for_replacement(which_admin)
+        except ContractPanic:
+            self._write_vote(voter, which_admin, previous)      # reverted transaction: nothing is stored
+            raise
+
+    def _write_vote(self, emitter: int, receiver: int, value: bool) -> None:
+        if receiver < len(self.admins):
+            self.vote_matrix[emitter][receiver] = value
+        else:
+            self._stray_votes[(emitter, receiver)] = value
 
     def _check_for_replacement(self, which: int) -> None:
-        votes = sum(1 for i in range(len(self.admins)) if self.vote_matrix[i][which])
+        a = len(self.admins)
+        if which < a:
+            votes = sum(1 for i in range(a) if self.vote_matrix[i][which])
+        else:
+            votes = sum(1 for i in range(a) if self._stray_votes.get((i, which), False))
         if self.required_majority > votes:
             return
-        prop = self.replacement_propositions[which]
+        prop = self.replacement_propositions[which] if which < a else None   # storage default: Option::None
         if prop is None:
             raise ContractPanic("Option::unwrap failed")        # `.unwrap()` on an empty proposition
         self.oracle_addresses[prop[0]] = prop[1]

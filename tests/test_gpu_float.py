@@ -30,7 +30,9 @@ def test_notebook_golden(golden):
             # the reference's mask: exact, except that oracles whose deviation sits within rounding of the
             # cut may swap sides in fp32
             safe = masks_equal_up_to_cut_ties(r["reliable"], golden[key + "_mask"], r["qr"].astype(np.float64), n, f, 10 * RTOL[dt])
-            assert safe.mean() > 0.75
+            # measured: no round differs in fp64; in fp32 (inputs rounded to fp32) a few per cent of these tiny batches
+            print(f"{key} {dt}: {1 - safe.mean():.4f} of the rounds excluded")
+            assert safe.mean() >= (0.999 if dt == torch.float64 else 0.95)
             np.testing.assert_allclose(r["consensus"][safe], golden[key + "_consensus"][safe], rtol=RTOL[dt], atol=1e-7)
             # rank_array (ipynb :342-352): rank 0 = largest deviation
             ranks = (n - 1) - np.argsort(np.argsort(r["qr"], axis=1, kind="stable"), axis=1, kind="stable")
@@ -87,13 +89,36 @@ def test_float_vs_oracle(N, D, F, dt, mode):
     np.testing.assert_allclose(r["qr"], ora["qr"], rtol=10 * rt, atol=1e-9)
     np.testing.assert_allclose(r["rel1"], ora["rel1"], rtol=rt, atol=10 * rt)
     same = masks_equal_up_to_cut_ties(r["reliable"], ora["reliable"], ora["qr"], N, F, 20 * rt)
-    assert same.mean() >= 0.5
+    # identical inputs in both precisions: fp64 agrees on every round; fp32 may flip an oracle whose risk is within
+    # rounding of the cut (measured: none on these batches; test_gpu_bulk_parity.py prints the bulk fractions)
+    print(f"{N}x{D} {dt} {mode}: {1 - same.mean():.4f} of the rounds excluded")
+    assert same.mean() >= (0.999 if dt == torch.float64 else 0.97)
     safe = same
     np.testing.assert_allclose(r["consensus"][safe], ora["consensus"][safe], rtol=rt, atol=1e-7)
     np.testing.assert_allclose(r["rel2"][safe], ora["rel2"][safe], rtol=rt, atol=10 * rt)
     mt = 1e-6 if dt == torch.float64 else 2e-2   # z-scores amplify fp32 rounding
     np.testing.assert_allclose(r["skew"][safe], ora["skew"][safe], rtol=mt, atol=mt)
     np.testing.assert_allclose(r["kurt"][safe], ora["kurt"][safe], rtol=mt, atol=10 * mt)
+
+
+@pytest.mark.parametrize("N,D", [(7, 2), (20, 3), (64, 16), (100, 5)])
+def test_single_kept_oracle_is_valid_for_median_and_mean(N, D):
+    """F = N - 1: restricted_median over ONE kept oracle is that oracle's vector (ipynb beta :369-371); only the
+    contract's smooth median (sorted[mid - 1], math.cairo:117) needs two rows and reports status 5."""
+    import svoc
+    from oracle import cref
+    rng = np.random.default_rng(seed_of("single", N, D))
+    x = rng.beta(10, 15, (50, N, D))
+    for centre, tie in ((1, 1), (2, 0)):
+        ora = cref.float_batch(x, N - 1, centre=centre, tie=tie, want_moments=False)
+        r = _np(svoc.consensus_float(torch.from_numpy(x).cuda(), N - 1, centre=centre, tie_rule=tie))
+        assert np.all(r["status"] == 0)
+        assert np.array_equal(r["reliable"], ora["reliable"]) and np.all(r["reliable"].sum(axis=1) == 1)
+        np.testing.assert_allclose(r["consensus"], ora["consensus"], rtol=1e-12)
+        np.testing.assert_allclose(r["consensus"], x[r["reliable"]], rtol=1e-12)
+        np.testing.assert_allclose(r["rel2"], ora["rel2"], rtol=1e-9, atol=1e-9)
+    r = _np(svoc.consensus_float(torch.from_numpy(x).cuda(), N - 1, centre=0))
+    assert np.all(r["status"] == 5)
 
 
 def test_ties_follow_the_rule():

@@ -202,3 +202,49 @@ def test_batched_epoch_replay_matches_sequential_contract(kind):
         assert n_reverts > 0 and rp.passes > 1
     else:
         assert rp.passes == 1
+
+
+@pytest.mark.parametrize("kind", ["beta", "tiny", "coarse"])
+def test_batched_epoch_replay_matches_the_bigint_oracle(kind):
+    """f2 against oracle/ (not against the repo's own contract mirror): the stored vectors are walked one commit
+    at a time in plain Python, every candidate state goes through oracle/fixed_oracle.consensus_round (big-int
+    restatement of contract.cairo:442-503), a panicking commit is dropped (the transaction reverts,
+    contract.cairo:331-343 never ran) — and the batched replay must report the same reverts, panic codes and
+    getter values after every commit."""
+    import numpy as np
+    import svoc
+    from helpers import gen_fixed
+    from oracle import fixed_oracle as fo
+    rng = np.random.default_rng(23)
+    E, N, D, F = 8, 7, 3, 2
+    prev = gen_fixed("beta", rng, E, N, D)
+    new = gen_fixed(kind, rng, E, N, D)
+    if kind == "coarse":                                   # a few commits outside [0, W]: interval panics
+        new[::2, 3, 1] = -5
+    order = np.stack([rng.permutation(N) for _ in range(E)])
+    rp = svoc.replay_epochs(torch.from_numpy(prev).cuda(), torch.from_numpy(new).cuda(), F, constrained=True,
+                            order=torch.from_numpy(order).cuda())
+    n_reverts = 0
+    for e in range(E):
+        state = [list(map(int, row)) for row in prev[e]]
+        last = None
+        for k in range(N):
+            i = int(order[e, k])
+            cand = [list(r) for r in state]
+            cand[i] = list(map(int, new[e, i]))
+            o = fo.consensus_round(cand, F, True, 0, True)
+            if o.status != 0:
+                n_reverts += 1
+                assert bool(rp.reverted[e, k]) and int(rp.revert_status[e, k]) == o.status, (e, k, o.status)
+            else:
+                assert not bool(rp.reverted[e, k]), (e, k)
+                state, last = cand, o
+            got = rp.after_commit(e, k)
+            if last is None:
+                assert got == {}
+                continue
+            assert int(got["rel1"]) == last.rel1 and int(got["rel2"]) == last.rel2
+            assert got["consensus"].tolist() == last.consensus and got["reliable"].tolist() == last.reliable
+            assert got["skew"].tolist() == last.skew and got["kurt"].tolist() == last.kurt
+    if kind != "beta":
+        assert n_reverts > 0

@@ -57,6 +57,12 @@ def test_contract_mirror_gate_and_vote_without_gpu():
     c.set_caller(admins[1])
     with pytest.raises(ContractPanic):
         c.vote_for_a_proposition(1, True)                # majority reached on an empty proposition: unwrap panics
+    assert not c.vote_matrix[1][1] and c.vote_matrix[0][1]   # the reverted transaction left no vote behind
+    c.vote_for_a_proposition(7, True)                    # a receiver beyond the admin list: a storage map takes any key
+    c.set_caller(admins[2])
+    with pytest.raises(ContractPanic):
+        c.vote_for_a_proposition(7, True)                # second vote at that key: majority on a proposition that is None
+    assert c._stray_votes == {(1, 7): True, (2, 7): False}
     d = OracleConsensusNDS(admins, False, 2, 2, True, 0, 2, oracles)
     d.set_caller(admins[0])
     with pytest.raises(ContractPanic):
