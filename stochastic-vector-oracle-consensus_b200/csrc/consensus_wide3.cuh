@@ -95,12 +95,33 @@ __device__ __forceinline__ void tma_load_box(void *dst, const CUtensorMap *map, 
         : "memory");
 }
 
+// if (flag) { [slot] = v; slot += one candidate slot; } without a branch
+__device__ __forceinline__ void store_if(uint32_t &slot, unsigned flag, float v) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.f32 [%0], %2;\n\t@p add.u32 %0, %0, 256;\n\t}"
+                 : "+r"(slot) : "r"(flag), "f"(v) : "memory");
+}
+__device__ __forceinline__ void store_if(uint32_t &slot, unsigned flag, int32_t v) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.s32 [%0], %2;\n\t@p add.u32 %0, %0, 256;\n\t}"
+                 : "+r"(slot) : "r"(flag), "r"(v) : "memory");
+}
+static_assert(W3_COLS * 4 == 256, "store_if advances by one candidate slot");
+
+// the exact, slow column centre as a real call: it is reached only by degenerate columns, and inlining its four
+// call sites would add a sixth to the kernel's code
+template <class Tr>
+__device__ __noinline__ typename Tr::val_t w3_exact_centre(const typename Tr::in_t *gcol, int N, const uint8_t *keep,
+                                                           int n_valid, int kind) {
+    typename Tr::val_t sk, ku;
+    int stw = STW_OK;
+    return column_centre_generic<Tr>(gcol, W3_D, N, keep, n_valid, kind, false, sk, ku, stw);
+}
+
 // ---- keys in registers
-template <class Tr, bool FIRST, bool FULL>
+template <class Tr, bool FIRST, bool FULL, bool ONLY_VALID>
 __device__ __forceinline__ void w3_build_keys(const typename Tr::in_t (&x)[W3_NV], unsigned (&kw)[W3_NKW], int N, int part,
                                               typename Tr::in_t lo, typename Tr::in_t hi,
-                                              const typename WideKey<Tr>::Scale &sc, bool only_valid) {
-    // only_valid: rows whose current key is the sentinel (dropped / padded) keep it
+                                              const typename WideKey<Tr>::Scale &sc) {
+    // ONLY_VALID: rows whose current key is the sentinel (dropped / padded) keep it
 #pragma unroll
     for (int q = 0; q < W3_NKW; ++q) {
         unsigned f[4];
@@ -108,9 +129,9 @@ __device__ __forceinline__ void w3_build_keys(const typename Tr::in_t (&x)[W3_NV
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             const int j = 4 * q + b;
-            f[b] = wide_key<Tr, FIRST>(x[j], lo, hi, sc) & 0xffu;
+            f[b] = wide_key<Tr, FIRST>(x[j], lo, hi, sc);        // pack4 takes the low byte
             if (!FULL && w3_row(j, part) >= N) f[b] = 127u;
-            if (only_valid && ((old >> (8 * b)) & 0xffu) == 127u) f[b] = 127u;
+            if (ONLY_VALID && ((old >> (8 * b)) & 0xffu) == 127u) f[b] = 127u;
         }
         kw[q] = pack4(f[0], f[1], f[2], f[3]);
     }
@@ -154,11 +175,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
     using Key = WideKey<Tr>;
     refined = false;
     if (col_const) return Tr::half_sum((val_t)const_value, (val_t)const_value);
-    if (col_fallback) {
-        val_t sk, ku;
-        int stw = STW_OK;
-        return column_centre_generic<Tr>(gcol, W3_D, w.N, keep, n_valid, kind, false, sk, ku, stw);
-    }
+    if (col_fallback) return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
     int klo, khi;
     centre_ranks(kind, n_valid, klo, khi);
     in_t v_lo = const_value, v_hi = const_value;
@@ -199,17 +216,14 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
         bool rescue = false;
         in_t thr = const_value;
         if (m <= W3_CAP) {
-            // values of this part's window rows -> slots off.. (straight from the registers)
-            int k = off;
+            // values of this part's window rows -> slots off.. (straight from the registers).  Written as a test, a
+            // predicated store and a predicated address bump per value: left to itself the compiler branches
+            // around every store (a dozen instructions per element)
+            uint32_t slot = smem_u32(lc) + (uint32_t)off * (W3_COLS * 4);
 #pragma unroll
             for (int q = 0; q < W3_NKW; ++q) {
 #pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    if (fl[q] & (0x80u << (8 * b))) {
-                        lc[k * W3_COLS] = x[4 * q + b];
-                        ++k;
-                    }
-                }
+                for (int b = 0; b < 4; ++b) store_if(slot, fl[q] & (0x80u << (8 * b)), x[4 * q + b]);
             }
             __syncwarp(w.cmask);
             // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
@@ -273,11 +287,9 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 thr = a;
                 rescue = j2 >= m;
             } else if (!Key::make(a, b, sc)) {
-                val_t sk, ku;
-                int stw = STW_OK;
-                return column_centre_generic<Tr>(gcol, W3_D, w.N, keep, n_valid, kind, false, sk, ku, stw);
+                return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
             } else {
-                w3_build_keys<Tr, false, FULL>(x, kw, w.N, w.part, a, b, sc, true);
+                w3_build_keys<Tr, false, FULL, true>(x, kw, w.N, w.part, a, b, sc);
                 refined = true;
                 continue;
             }
@@ -323,7 +335,7 @@ __host__ __device__ inline W3Smem w3_smem_layout(size_t vs) {
     s.misc = take(16, 16);                                // stw, sel
     s.keep = take(W3_ROWS, 16);
     s.bar = take(16, 16);
-    s.total = off + 1024;                                 // slack for aligning the dynamic base
+    s.total = off;
     return s;
 }
 
@@ -334,8 +346,8 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
     using Key = WideKey<Tr>;
-    extern __shared__ unsigned char smem_dyn[];
-    unsigned char *smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
+    extern __shared__ __align__(1024) unsigned char smem_w3[];     // the 128-byte swizzle wants the boxes 1024-aligned
+    unsigned char *const smem_raw = smem_w3;
     const W3Smem S = w3_smem_layout(sizeof(acc_t));
     const int N = FULL ? W3_ROWS : p.N, R = p.R;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -377,6 +389,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
 
     const uint32_t tile_bytes = 2 * W3_BOX_BYTES;
     if (tid == 0) {
+        if (smem_u32(tile_s) & 1023u) __trap();      // the swizzle pattern is a function of the address bits
         mbar_init(bar, 1);
         if (cluster_id < p.T) {
             mbar_expect_tx(bar, tile_bytes);
@@ -408,7 +421,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
             x[2 * k + 1] = src1[k * 256];
         }
         // ---- phase 1a: key scale from a 64-row sample (rows 0..63: the first 16 values of every part) and the keys
-        bool col_const = false, col_fb = false, refined1 = false, refined2 = false;
+        bool col_const = false, col_fb = false, refined1 = false;
         in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
         typename Key::Scale sc{};
 #pragma unroll
@@ -431,10 +444,19 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
         }
         col_const = !(hi > lo);
         col_fb = !col_const && !Key::make(lo, hi, sc);
+        if (col_fb) {
+            // No keys will be built, so nothing below has read values 16..63 yet.  They must have ARRIVED in their
+            // registers before the barrier that hands the landing buffer to the next copy: fold them into a word
+            // the compiler has to produce (the store never happens).
+            uint32_t fold = 0;
+#pragma unroll
+            for (int j = 16; j < W3_NV; ++j) fold ^= okey(x[j]);
+            if (fold == 0x9e3779b9u && p.T < 0) *sel_s = (int)fold;
+        }
         unsigned kw[W3_NKW];
 #pragma unroll
         for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
-        if (!col_const && !col_fb) w3_build_keys<Tr, true, FULL>(x, kw, N, part, lo, hi, sc, false);
+        if (!col_const && !col_fb) w3_build_keys<Tr, true, FULL, false>(x, kw, N, part, lo, hi, sc);
         // every value has been consumed: the landing buffer is free for the next round, whose copy now has the
         // whole of this round's computation to arrive
         __syncthreads();
@@ -445,9 +467,21 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
             tma_load_box(tile_s, &tmap, (int)rank * W3_COLS, row0, bar);
             tma_load_box(tile_s + W3_BOX_BYTES / 4, &tmap, (int)rank * W3_COLS + 32, row0, bar);
         }
-        // ---- phase 1b: first-pass centre of this thread's column
-        const val_t e1 = w3_centre<Tr, FULL>(w, x, kw, gcol, nullptr, N, p.centre, col_const, col_fb, lo, lc, refined1);
-        if (part == 0 && p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * W3_D + gc] = e1;
+        // ---- the two passes share ONE inlined copy of the centre code (the kernel is 250 KB of SASS otherwise):
+        //      pass 0 = first-pass centre, risks, row selection, key patching; pass 1 = second-pass centre
+        val_t e1 = 0;
+#pragma unroll 1
+        for (int pass = 0;; ++pass) {
+            bool refined = false;
+            const val_t ctr = w3_centre<Tr, FULL>(w, x, kw, gcol, pass ? keep_s : nullptr, pass ? R : N,
+                                                  pass ? p.centre2 : p.centre, col_const, col_fb, lo, lc, refined);
+            if (pass) {
+                if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = ctr;
+                break;
+            }
+            e1 = ctr;
+            refined1 = refined;
+            if (part == 0 && p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * W3_D + gc] = e1;
 
         // ---- phase 2: quadratic risk.  A thread holds (x - e1)^2 of 64 rows of ONE column; the 8 columns of the
         //      warp are folded with a transposing shuffle tree (lane bit 0 keeps the rows of its own parity, bits 1
@@ -534,6 +568,12 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
 #pragma unroll
                     for (int j = 0; j < NS; ++j) mw = lane == j ? words[j] : mw;
                     if (lane < NS) maskw[lane] = mw;
+                    __syncwarp();
+                    // keep flags as bytes for the exact fallbacks: bit b of a mask byte -> byte b (0 / 1)
+                    const unsigned bits8 = (maskw[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
+                    const unsigned lo4 = ((bits8 & 0xfu) * 0x00204081u) & 0x01010101u;
+                    const unsigned hi4 = ((bits8 >> 4) * 0x00204081u) & 0x01010101u;
+                    *reinterpret_cast<uint2 *>(keep_s + 8 * lane) = make_uint2(lo4, hi4);
                 }
                 if (lane == 0) *sel_s = fast ? 1 : 0;
             } else if (warp == 1) {
@@ -565,18 +605,14 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                     const acc_t q = qr_s[j];
                     rk += (q < mineq) | ((q == mineq) & (high ? j > tid : j < tid));
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, tid < N && rk < R);
+                const bool kept = tid < N && rk < R;
+                keep_s[tid] = kept ? 1 : 0;
+                const unsigned bal = __ballot_sync(0xffffffffu, kept);
                 if (lane == 0) maskw[warp] = bal;
                 __syncthreads();
             }
-            // keep flags as bytes (exact fallbacks walk them), second-pass reliability, mask and status
+            // second-pass reliability, mask and status
             if (warp == 0) {
-                for (int g = lane; g * 8 < W3_ROWS; g += 32) {
-                    const unsigned bits8 = (maskw[g >> 2] >> (8 * (g & 3))) & 0xffu;
-                    const unsigned lo4 = ((bits8 & 0xfu) * 0x00204081u) & 0x01010101u;
-                    const unsigned hi4 = ((bits8 >> 4) * 0x00204081u) & 0x01010101u;
-                    *reinterpret_cast<uint2 *>(keep_s + 8 * g) = make_uint2(lo4, hi4);
-                }
                 acc_t s2 = 0;
 #pragma unroll
                 for (int j = 0; j < NS; ++j)
@@ -609,37 +645,32 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                     }
                 }
             }
-            // the column warps need the flag bytes only in the exact fallbacks, but warp 0 writes them after the
-            // barrier above: those paths (col_fb, Key::make failure inside w3_centre) are guarded below
         }
-        // ---- phase 4: second-pass centre over the kept rows
-        {
-            val_t cons = 0;
-            if (!shape2) {
-                if (!col_const && !col_fb) {
-                    if (refined1) {
-                        // the first pass re-keyed the column: back to the first-pass scale, dropped rows -> sentinel
+        // ---- phase 4 set-up: keys of the kept rows only; the loop then runs the second-pass centre
+            if (shape2) {
+                if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = 0;
+                break;
+            }
+            if (!col_const && !col_fb) {
+                if (refined1) {
+                    // the first pass re-keyed the column: back to the first-pass scale, dropped rows -> sentinel
 #pragma unroll
-                        for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
-                        w3_build_keys<Tr, true, FULL>(x, kw, N, part, lo, hi, sc, false);
-                    }
-                    // dropped rows of this thread -> sentinel key.  Key word q holds rows 32*(q>>1) + 16*(q&1) +
-                    // {0, 1, 8, 9} + 2*part: two bit pairs of mask word q>>1, spread to four bytes by one multiply
+                    for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
+                    w3_build_keys<Tr, true, FULL, false>(x, kw, N, part, lo, hi, sc);
+                }
+                // dropped rows of this thread -> sentinel key.  Key word q holds rows 32*(q>>1) + 16*(q&1) +
+                // {0, 1, 8, 9} + 2*part: two bit pairs of mask word q>>1, spread to four bytes by one multiply
 #pragma unroll
-                    for (int g = 0; g < W3_NKW / 2; ++g) {
-                        const unsigned drop = ~maskw[g] >> (2 * part);
+                for (int g = 0; g < W3_NKW / 2; ++g) {
+                    const unsigned drop = ~maskw[g] >> (2 * part);
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            const unsigned t = drop >> (16 * h);
-                            const unsigned nib = (t & 3u) | ((t >> 6) & 0xcu);
-                            kw[2 * g + h] |= ((nib * 0x00204081u) & 0x01010101u) * 0x7fu;
-                        }
+                    for (int h = 0; h < 2; ++h) {
+                        const unsigned t = drop >> (16 * h);
+                        const unsigned nib = (t & 3u) | ((t >> 6) & 0xcu);
+                        kw[2 * g + h] |= ((nib * 0x00204081u) & 0x01010101u) * 0x7fu;
                     }
                 }
-                // exact fallbacks read keep_s: written by warp 0 after the last barrier, so wait for it there only
-                cons = w3_centre<Tr, FULL>(w, x, kw, gcol, keep_s, R, p.centre2, col_const, col_fb, lo, lc, refined2);
             }
-            if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = cons;
         }
     }
 }

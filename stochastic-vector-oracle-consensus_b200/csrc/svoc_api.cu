@@ -8,7 +8,7 @@
 #include <algorithm>
 #include <cstdlib>
 
-#include "consensus_wide2.cuh"
+#include "consensus_wide3.cuh"
 #include "montecarlo.cuh"
 
 namespace svoc {
@@ -118,8 +118,45 @@ static bool plan_wide2(const svoc_config &c, const void *pred, Plan &pl) {
     return true;
 }
 
-static Plan make_plan(const svoc_config &c, const void *pred, int64_t T) {
+// wide3 variant: the round in registers, split by columns over a 2-CTA cluster, fetched by TMA tensor-map copies.
+// Covers the hot shape (D = 128, N <= 256, 32-bit elements, median centres, no moments / rank output); everything
+// else goes to wide2.
+static bool plan_wide3(const svoc_config &c, const void *pred, const svoc_outputs *out, int64_t T, Plan &pl) {
+    const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
+    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
+    if (N <= 64 || N > W3_ROWS || D != W3_D || R < 2 || c.n_failing < 0) return false;
+    const std::string &force = forced_variant();
+    if (!force.empty() && force != "wide3") return false;
+    if (c.want_moments || (out && out->rank)) return false;
+    const int centre2 = c.centre2 == SVOC_CENTRE_DEFAULT ? (c.constrained ? c.centre : SVOC_CENTRE_MEAN) : c.centre2;
+    if (c.centre == SVOC_CENTRE_MEAN || centre2 == SVOC_CENTRE_MEAN) return false;
+    if ((reinterpret_cast<uintptr_t>(pred) & 15) != 0) return false;
+    if ((long long)T * N > 0x7fffffffLL) return false;                  // TMA row coordinates are 32-bit
+    pl.variant = 4;
+    pl.smem = w3_smem_layout(c.dtype == SVOC_F32 ? 4 : 8).total;
+    pl.threads = W3_THREADS;
+    pl.rb = 1;
+    pl.npad = 0;
+    pl.tile_smem = 1;
+    pl.wP = 4; pl.wRP = 64; pl.wCS = 0; pl.wH = 1;
+    pl.grid = 2 * std::min<long long>(T, (long long)sm_count());      // clusters of two CTAs, two CTAs per SM
+    return true;
+}
+
+W3EncodeFn w3_encode_fn() {
+    static W3EncodeFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return reinterpret_cast<W3EncodeFn>(f);
+    }();
+    return fn;
+}
+
+static Plan make_plan(const svoc_config &c, const void *pred, const svoc_outputs *out, int64_t T) {
     Plan pl{};
+    if (plan_wide3(c, pred, out, T, pl)) return pl;
     if (plan_wide2(c, pred, pl)) {
         pl.grid = std::min<long long>(T, (long long)sm_count() * W2_CTAS_PER_SM);
         return pl;
@@ -200,7 +237,7 @@ int consensus_device(const svoc_config *cfg, const void *pred, int64_t T, const 
                      bool fixed) {
     if (int rc = validate(cfg, pred, T, out, fixed)) return rc;
     if (T == 0) return 0;
-    const Plan pl = make_plan(*cfg, pred, T);
+    const Plan pl = make_plan(*cfg, pred, out, T);
     const Params p = make_params(*cfg, pred, T, *out, pl);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (cfg->dtype) {
@@ -294,7 +331,8 @@ const char *svoc_kernel_variant(const svoc_config *cfg) {
     if (!cfg) return "invalid";
     const int np = svoc::npad_for(cfg->n_oracles);
     svoc::Plan pl{};
-    if (svoc::plan_wide2(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide2");
+    if (svoc::plan_wide3(*cfg, nullptr, nullptr, 1, pl)) snprintf(buf, sizeof buf, "wide3");
+    else if (svoc::plan_wide2(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide2");
     else if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
     else if (np) snprintf(buf, sizeof buf, "small%d", np);
     else snprintf(buf, sizeof buf, "generic");
