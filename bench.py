@@ -178,10 +178,19 @@ def cpu_port(wl, seconds=10.0, nthreads=0):
     cores = cref.max_threads() if nthreads <= 0 else nthreads
     key = (N, D, F, wl["dtype"])
     if key not in _CPU_BATCH:
+        # the same law the GPU arm draws (make_predictions): honest ~ beta(10, 15); failing oracles at random
+        # positions, uniform(0, 1) — or, config 4, colluding on one shared vector mode + 0.15
         rng = np.random.default_rng(0)
         T = int(max(cores * 8, min(2_000_000, (1 << 30) // (N * D * 8))))
         x = rng.beta(10, 15, (T, N, D))
-        x[:, :F, :] = rng.random((T, F, D))
+        pos = np.argsort(rng.random((T, N)), axis=1)[:, :F]                      # a random F-subset per round
+        bad = np.zeros((T, N), dtype=bool)
+        np.put_along_axis(bad, pos, True, axis=1)
+        if wl is WORKLOADS["c4"]:
+            x[bad] = (10.0 - 1.0) / (10.0 + 15.0 - 2.0) + 0.15
+        else:
+            x[bad] = rng.random((int(bad.sum()), D))
+        x = x.astype(np.float32).astype(np.float64)                               # what the fp32 arm sees
         _CPU_BATCH[key] = (x * 1e6).astype(np.int64) if wl["dtype"] == "i32" else x
     x = _CPU_BATCH[key]
     T = x.shape[0]
@@ -216,6 +225,51 @@ def numpy_restatement_rate(wl, seconds=2.0):
     return n / (time.perf_counter() - t0)
 
 
+def c2_sweep(torch, svoc, dev, T=1_000_000):
+    """BASELINE config 2: failing-oracle fraction sweep 0-40 % at N = 7, D = 2.  Honest oracles ~
+    beta(a = 10, b = (15, 30)) as generate_2d_beta_oracles draws them (ipynb beta :49-68), failing ones uniform(0, 1) at
+    random positions.  (a) exactly F = 0, 1, 2 failing oracles, the contract's n_failing set to F; (b) every oracle
+    failing independently with probability p, n_failing fixed at 2 (documentation/README.md:105-114).  Notebook
+    semantics (true median, lower index kept at ties); per point: rounds/s of the consensus kernel, the benchmark()
+    figures of ipynb beta :385-402 (identification success = exact mask equality; true consensus reliability =
+    100 (1 - 2 mean ||consensus - median of the honest rows||)) and the share of failing oracles flagged unreliable."""
+    N, D = 7, 2
+    out = []
+    points = [("exact", f, 0.0) for f in (0, 1, 2)] + [("bernoulli", 2, p) for p in (0.0, 0.1, 0.2, 0.3, 0.4)]
+    for mode, F, prob in points:
+        gen_f = F if mode == "exact" else (0 if prob == 0.0 else 2)
+        g = svoc.generate(T, N, D, gen_f, a=10.0, b=(15.0, 30.0), failing="uniform", seed=4242, dtype=torch.float32,
+                          device=dev, failing_prob=prob)
+        run = lambda: svoc.consensus_float(g.pred, F, centre=svoc.CENTRE_MEDIAN, tie_rule=svoc.TIE_LOW_INDEX_KEPT,  # noqa: E731
+                                           want_moments=False, want_qr=False, want_essence=False)
+        for _ in range(3):
+            r = run()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(5):
+            r = run()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 5
+        honest, kept = g.honest, r.reliable
+        h = honest.sum(dim=1)
+        srt = torch.where(honest.unsqueeze(-1), g.pred, torch.full_like(g.pred, float("inf"))).sort(dim=1).values
+        idx_lo = ((h - 1).clamp(min=0) // 2).view(-1, 1, 1).expand(-1, 1, D)
+        idx_hi = (h // 2).clamp(max=N - 1).view(-1, 1, 1).expand(-1, 1, D)
+        truth = 0.5 * (srt.gather(1, idx_lo) + srt.gather(1, idx_hi)).squeeze(1)
+        ok = h > 0
+        dist = (r.consensus - truth)[ok].norm(dim=1).mean().item()
+        n_fail = (~honest).sum().item()
+        out.append({"mode": mode, "n_failing": F, "failing_prob": prob, "failing_fraction": (N - h.float().mean().item()) / N,
+                    "rounds_per_s": T / (ms * 1e-3), "ms_per_step": ms,
+                    "identification_success_pct": 100.0 * (kept == honest).all(dim=1).float().mean().item(),
+                    "failing_flagged_pct": 100.0 * ((~kept) & (~honest)).sum().item() / n_fail if n_fail else None,
+                    "true_consensus_reliability_pct": 100.0 * (1 - 2 * dist)})
+        del g, r, srt, truth
+    return out
+
+
 def reference_arm(args, wl, rank):
     if rank != 0:
         return
@@ -235,7 +289,9 @@ def reference_arm(args, wl, rank):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if wl["dtype"] != "i32" else "int64", "data": "synthetic",
             "config": {"workload": wl["desc"], "n_oracles": wl["N"], "dimension": wl["D"], "n_failing": wl["F"],
-                       "note": "CPU port of the reference (oracle/svoc_ref.c): the reference itself is Cairo + a notebook and cannot run here"},
+                       "note": "CPU port of the reference (oracle/svoc_ref.c, gcc -O2 -march=native, selection instead of a full sort, "
+                               "all host threads): the reference itself is Cairo + a notebook and cannot run here; same law and "
+                               "failing model as the svoc arm (colluders for config 4), float64 arithmetic"},
             "cpu_baseline": base,
             "e2e": {"value": v, "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -456,6 +512,8 @@ def main():
         base, _, _ = cpu_port(wl, seconds=10.0)
         base["numpy_restatement_single_thread_rounds_per_s"] = numpy_restatement_rate(wl)
         line["cpu_baseline"] = base
+    if args.workload == "c2" and world == 1:
+        line["sweep"] = c2_sweep(torch, svoc, dev)
     if not args.no_secondary and world == 1:
         del x, xh, r, rh
         torch.cuda.empty_cache()
@@ -476,8 +534,13 @@ def main():
             torch.cuda.synchronize()
             ms = a.elapsed_time(b) / 3
             B2 = algorithmic_bytes_per_round(w2["N"], w2["D"], 4, 8 if w2["dtype"] == "i32" else 4)
+            gbs = w2["T"] * B2 / (ms * 1e-3) / 1e9
             sec[name] = {"workload": w2["desc"], "rounds_per_s": w2["T"] / (ms * 1e-3), "ms_per_step": ms,
-                         "algorithmic_GBps": w2["T"] * B2 / (ms * 1e-3) / 1e9, "frac_of_peak": w2["T"] * B2 / (ms * 1e-3) / 1e9 / peak}
+                         "kernel_variant": svoc.kernel_variant(w2["N"], w2["D"], x2.dtype),
+                         "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                                      "bytes_per_round": B2, "kernel_ms": ms, "algorithmic_bytes": w2["T"] * B2,
+                                      "note": None if w2["T"] * w2["N"] * w2["D"] * 4 > 1e9 else
+                                      "inputs fit in L2: the HBM fraction is not meaningful for this shape"}}
             del x2
             torch.cuda.empty_cache()
         line["secondary_workloads"] = sec

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SVOC_VERSION 100
+#define SVOC_VERSION 101
 
 /* element types of the prediction tensor */
 #define SVOC_I32 0
@@ -184,6 +184,10 @@ typedef struct svoc_gen_config {
     double shift;                 /* colluders' offset */
     uint64_t seed;
     int64_t trial_offset;         /* global index of the first trial of this call (multi-GPU sharding) */
+    double failing_prob;          /* 0: exactly n_failing oracles fail, at random positions (the notebook generators).
+                                     > 0: every oracle fails independently with this probability (the failing-fraction
+                                     sweep of BASELINE config 2; documentation/README.md:105-114 "an oracle is failing
+                                     with probability p"); n_failing is ignored by the generator then */
 } svoc_gen_config;
 
 /* pred: [T][N][D] of cfg->dtype on the device; honest (may be NULL): [T][ceil(N/32)] bit mask, bit = 1

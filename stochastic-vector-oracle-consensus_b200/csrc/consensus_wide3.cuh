@@ -6,21 +6,28 @@
 // `wide2` waiting on L2 round trips (every sweep after the first re-read the round from L2) and spending a
 // fifth of its instructions on loads, address arithmetic and shared-memory key traffic:
 //
-//   * A round is split by COLUMNS over a cluster of two CTAs (64 columns each, 256 threads, 128 registers):
-//     two CTAs — halves of two different rounds — share an SM and fill each other's barrier waits.
+//   * A round is split by COLUMNS over a cluster of two CTAs (64 columns each, 256 threads): two CTAs — halves
+//     of two different rounds — share an SM and fill each other's waits.
 //   * Each CTA's half round (256 rows x 64 columns, 64 KB) is fetched by two 2-D TMA tensor-map copies
-//     (cp.async.bulk.tensor, 128-byte swizzle, completing on an mbarrier) into a shared-memory landing buffer,
-//     and moved from there into REGISTERS: a thread owns 64 values of one column (rows 8k + 2*part + {0,1}; with
-//     the swizzle the 32 lanes of a warp read 32 different banks).  Keys (16 packed words) live in registers
-//     too.  As soon as every thread holds its values the buffer is free, so the NEXT round's copy is issued
-//     right then and lands while this round is being computed: HBM latency is never exposed, and after the
-//     one LDS per value nothing in the round touches global memory or L2 again except the outputs.
+//     (cp.async.bulk.tensor, 128-byte swizzle, completing on an mbarrier) into shared memory and STAYS there for
+//     the whole round: the key build reads it column-wise (a thread owns rows 8k + 2*part + {0,1} of one column;
+//     with the swizzle the 32 lanes of a warp hit 32 different banks), the risk sweep row-wise with 128-bit
+//     loads (a quarter-warp reads one 128-byte line), and the few window candidates of a column are fetched by
+//     row index.  Nothing in the round touches global memory or L2 again except the outputs.  The next round
+//     is pulled into L2 while this one is computed (cp.async.bulk.prefetch.tensor) and copied into shared memory
+//     as soon as the last thread has made its last read (an "empty" mbarrier), so the copy is an L2 hit whose
+//     latency the co-resident CTA covers.
+//   * Keys (16 packed words per thread) live in registers: the bisection has no memory traffic at all.
 //   * The per-oracle risks need all 128 columns: each CTA sums its 64 columns (a transposing shuffle tree over
-//     the 8 columns of a warp, then 8 warp partials per row through shared memory, fixed order), writes its 256
-//     partial sums into the PEER's shared memory (DSMEM) and one cluster barrier later both CTAs hold the same
-//     full risks — partial(rank 0) + partial(rank 1) on both sides, bit-identical — and select the same rows
-//     redundantly.  Partial buffers are double-buffered by round parity, so one cluster barrier per round is
-//     enough.
+//     the 16 lanes that share a row leaves every thread with ONE row total), sends its 256 partial sums into
+//     the PEER's shared memory with st.async, which completes on the peer's mbarrier — no cluster barrier, no
+//     fence — and both CTAs form partial(rank 0) + partial(rank 1), bit-identical, and select the same rows
+//     redundantly.  Buffers and barriers are double-buffered by round parity.
+//
+// A first version kept the round in REGISTERS (64 values per thread, 128 registers, the landing buffer freed
+// right after the key build): parity-green but 12.2 M rounds/s against 14.2 M for wide2 — window candidates had
+// to be extracted with a predicated store per element (registers cannot be indexed), which cost as much as the
+// loads it saved (profiles/r02b_*).
 //
 // Anything this kernel does not cover (moments, rank output, mean centres, other D, misaligned rounds) is
 // dispatched to `wide2`.  Reference semantics: see consensus_kernel.cuh (contract.cairo:442-503 etc.).
@@ -38,7 +45,10 @@ constexpr int W3_ROWS = 256;         // rows of a landing box (rows >= N are ign
 constexpr int W3_NV = 64;            // values per thread
 constexpr int W3_NKW = 16;           // packed key words per thread
 constexpr int W3_CAP = 32;           // candidate slots per column
+constexpr int W3_LSTRIDE = 36;       // words per column in the candidate list: 32 slots + 4 sentinels; 36 = 4 mod 32,
+                                     // so the 128-bit reads of the 8 columns of a warp fall into 8 different bank groups
 constexpr int W3_BOX_BYTES = 32 * W3_ROWS * 4;     // one 32-column box
+constexpr int W3_BOX_WORDS = W3_BOX_BYTES / 4;
 
 struct W3Ctx {
     int N;
@@ -73,18 +83,22 @@ __device__ __forceinline__ uint32_t map_to_peer(uint32_t smem_addr, uint32_t ran
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
     return r;
 }
-__device__ __forceinline__ void st_peer(uint32_t addr, float v) {
-    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+// store into the peer CTA's shared memory; the bytes are counted on the peer's mbarrier when they have landed
+__device__ __forceinline__ void st_async_peer(uint32_t addr, float v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(addr), "r"(__float_as_uint(v)), "r"(bar) : "memory");
 }
-__device__ __forceinline__ void st_peer(uint32_t addr, u64 v) {
-    asm volatile("st.shared::cluster.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+__device__ __forceinline__ void st_async_peer(uint32_t addr, u64 v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(addr), "l"(v), "r"(bar) : "memory");
 }
-__device__ __forceinline__ void st_peer(uint32_t addr, int v) {
-    asm volatile("st.shared::cluster.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+__device__ __forceinline__ void st_async_peer(uint32_t addr, uint32_t v, uint32_t bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(addr), "r"(v), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(u64 *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 // one box of the round: 32 columns x 256 rows starting at (col0, row0) of the [T*N][128] tensor
 __device__ __forceinline__ void tma_load_box(void *dst, const CUtensorMap *map, int col0, int row0, u64 *bar) {
@@ -94,19 +108,11 @@ __device__ __forceinline__ void tma_load_box(void *dst, const CUtensorMap *map, 
         "l"(map), "r"(col0), "r"(row0), "r"(smem_u32(bar))
         : "memory");
 }
-
-// if (flag) { [slot] = v; slot += one candidate slot; } without a branch
-__device__ __forceinline__ void store_if(uint32_t &slot, unsigned flag, float v) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.f32 [%0], %2;\n\t@p add.u32 %0, %0, 256;\n\t}"
-                 : "+r"(slot) : "r"(flag), "f"(v) : "memory");
+__device__ __forceinline__ void tma_prefetch_box(const CUtensorMap *map, int col0, int row0) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(col0), "r"(row0) : "memory");
 }
-__device__ __forceinline__ void store_if(uint32_t &slot, unsigned flag, int32_t v) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p st.shared.s32 [%0], %2;\n\t@p add.u32 %0, %0, 256;\n\t}"
-                 : "+r"(slot) : "r"(flag), "r"(v) : "memory");
-}
-static_assert(W3_COLS * 4 == 256, "store_if advances by one candidate slot");
 
-// the exact, slow column centre as a real call: it is reached only by degenerate columns, and inlining its four
+// the exact, slow column centre as a real call: it is reached only by degenerate columns, and inlining its
 // call sites would add a sixth to the kernel's code
 template <class Tr>
 __device__ __noinline__ typename Tr::val_t w3_exact_centre(const typename Tr::in_t *gcol, int N, const uint8_t *keep,
@@ -116,12 +122,20 @@ __device__ __noinline__ typename Tr::val_t w3_exact_centre(const typename Tr::in
     return column_centre_generic<Tr>(gcol, W3_D, N, keep, n_valid, kind, false, sk, ku, stw);
 }
 
+// this thread's value j (row 8*(j>>1) + 2*part + (j&1)) in the swizzled tile
+template <class in_t>
+__device__ __forceinline__ in_t w3_value(const in_t *src0, const in_t *src1, int j) {
+    return ((j & 1) ? src1 : src0)[(j >> 1) * 256];
+}
+
 // ---- keys in registers
-template <class Tr, bool FIRST, bool FULL, bool ONLY_VALID>
-__device__ __forceinline__ void w3_build_keys(const typename Tr::in_t (&x)[W3_NV], unsigned (&kw)[W3_NKW], int N, int part,
+// FROM_REGS: the values are passed in x (first build of a round); otherwise they are read from the tile.
+// ONLY_VALID: rows whose current key is the sentinel (dropped / padded) keep it.
+template <class Tr, bool FIRST, bool FULL, bool ONLY_VALID, bool FROM_REGS>
+__device__ __forceinline__ void w3_build_keys(const typename Tr::in_t *x, const typename Tr::in_t *src0,
+                                              const typename Tr::in_t *src1, unsigned (&kw)[W3_NKW], int N, int part,
                                               typename Tr::in_t lo, typename Tr::in_t hi,
                                               const typename WideKey<Tr>::Scale &sc) {
-    // ONLY_VALID: rows whose current key is the sentinel (dropped / padded) keep it
 #pragma unroll
     for (int q = 0; q < W3_NKW; ++q) {
         unsigned f[4];
@@ -129,7 +143,8 @@ __device__ __forceinline__ void w3_build_keys(const typename Tr::in_t (&x)[W3_NV
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             const int j = 4 * q + b;
-            f[b] = wide_key<Tr, FIRST>(x[j], lo, hi, sc);        // pack4 takes the low byte
+            const typename Tr::in_t xv = FROM_REGS ? x[j] : w3_value(src0, src1, j);
+            f[b] = wide_key<Tr, FIRST>(xv, lo, hi, sc);        // pack4 takes the low byte
             if (!FULL && w3_row(j, part) >= N) f[b] = 127u;
             if (ONLY_VALID && ((old >> (8 * b)) & 0xffu) == 127u) f[b] = 127u;
         }
@@ -161,15 +176,21 @@ __device__ __forceinline__ int w3_count_ge(const unsigned (&kw)[W3_NKW], unsigne
     return (int)((unsigned)(sum_keys + W3_NV * (int)(128u - cand) - ((a0 + a1) + (a2 + a3))) >> 8);
 }
 
+template <class T> __device__ __forceinline__ T w3_never_less();
+template <> __device__ __forceinline__ float w3_never_less<float>() { return __int_as_float(0x7f800000); }
+template <> __device__ __forceinline__ int32_t w3_never_less<int32_t>() { return 0x7fffffff; }
+
 // Centre of the valid rows of this thread's column (valid = key != sentinel: all rows < N in the first pass, the
 // kept rows in the second).  Executed by the four lanes of the column together; every one returns the result.
-// gcol / keep serve only the rare exact fallback, which walks the column in global memory.
+// src0 / src1: this thread's even / odd rows in the tile.  gcol / keep serve only the rare exact fallback, which
+// walks the column in global memory.  lcw: this column's candidate list (W3_LSTRIDE words).
 template <class Tr, bool FULL>
-__device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const typename Tr::in_t (&x)[W3_NV],
-                                                        unsigned (&kw)[W3_NKW], const typename Tr::in_t *gcol,
-                                                        const uint8_t *keep, int n_valid, int kind, bool col_const,
-                                                        bool col_fallback, typename Tr::in_t const_value,
-                                                        typename Tr::in_t *lc, bool &refined) {
+__device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const typename Tr::in_t *src0,
+                                                        const typename Tr::in_t *src1, unsigned (&kw)[W3_NKW],
+                                                        const typename Tr::in_t *gcol, const uint8_t *keep, int n_valid,
+                                                        int kind, bool col_const, bool col_fallback,
+                                                        typename Tr::in_t const_value, typename Tr::in_t *lcw,
+                                                        bool &refined) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using Key = WideKey<Tr>;
@@ -193,17 +214,19 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             if (lt <= klo) { prefix = cand; L = lt; }
             else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
         }
-        // ---- the window: the bucket of rank klo alone when rank khi is inside it, else that and the next two
+        // ---- the window: the bucket of rank klo alone when rank khi is inside it, else that and the next two.
+        //      One bit per value: the byte MSBs of a key word are gathered into a nibble by one multiply
+        //      (bits 7, 15, 23, 31 -> 28..31), 16 nibbles make the 64-bit mask of this thread's window rows.
         const unsigned span = (khi < LE) ? 1u : 3u;
         const unsigned up = prefix + span > 127u ? 127u : prefix + span;
         const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
-        unsigned fl[W3_NKW];                      // byte MSB set <=> that key is inside the window
-        int mine = 0;
+        unsigned wm[2] = {0u, 0u};
 #pragma unroll
         for (int q = 0; q < W3_NKW; ++q) {
-            fl[q] = (kw[q] + c1b) & ~(kw[q] + c2b) & 0x80808080u;
-            mine += __popc(fl[q]);
+            const unsigned fl = (kw[q] + c1b) & ~(kw[q] + c2b) & 0x80808080u;
+            wm[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
         }
+        const int mine = __popc(wm[0]) + __popc(wm[1]);
         // slot offset of this part = candidates of the lower parts; m = all of them
         int off = 0, m = 0;
 #pragma unroll
@@ -216,14 +239,20 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
         bool rescue = false;
         in_t thr = const_value;
         if (m <= W3_CAP) {
-            // values of this part's window rows -> slots off.. (straight from the registers).  Written as a test, a
-            // predicated store and a predicated address bump per value: left to itself the compiler branches
-            // around every store (a dozen instructions per element)
-            uint32_t slot = smem_u32(lc) + (uint32_t)off * (W3_COLS * 4);
+            // values of this part's window rows -> slots off.., fetched from the tile by row index
+            int k = off;
 #pragma unroll
-            for (int q = 0; q < W3_NKW; ++q) {
-#pragma unroll
-                for (int b = 0; b < 4; ++b) store_if(slot, fl[q] & (0x80u << (8 * b)), x[4 * q + b]);
+            for (int h = 0; h < 2; ++h) {
+                unsigned bits = wm[h];
+                while (bits) {
+                    const int pos = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    lcw[k++] = w3_value(src0, src1, 32 * h + pos);
+                }
+            }
+            if (w.part == 0) {                    // four sentinels behind the last candidate: the ranking reads 4 slots a trip
+                const in_t big = w3_never_less<in_t>();
+                lcw[m] = big; lcw[m + 1] = big; lcw[m + 2] = big; lcw[m + 3] = big;
             }
             __syncwarp(w.cmask);
             // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
@@ -234,14 +263,19 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
 #pragma unroll
                 for (int t = 0; t < W2_RANKW; ++t) {
                     const int a = base + t * 4;
-                    v[t] = a < m ? lc[a * W3_COLS] : lc[base * W3_COLS];
+                    v[t] = lcw[a < m ? a : base];
                     rr[t] = 0;
                 }
 #pragma unroll 1
-                for (int b = 0; b < m; ++b) {
-                    const in_t u = lc[b * W3_COLS];
+                for (int b = 0; b < m; b += 4) {
+                    const int4 raw = *reinterpret_cast<const int4 *>(lcw + b);
+                    in_t u[4];
+                    memcpy(u, &raw, 16);
 #pragma unroll
-                    for (int t = 0; t < W2_RANKW; ++t) count_lt(rr[t], u, v[t]);
+                    for (int s = 0; s < 4; ++s) {
+#pragma unroll
+                        for (int t = 0; t < W2_RANKW; ++t) count_lt(rr[t], u[s], v[t]);
+                    }
                 }
 #pragma unroll
                 for (int t = 0; t < W2_RANKW; ++t) {
@@ -256,8 +290,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             auto imax = [](int a, int b) { return a > b ? a : b; };
             b1 = w3_col_reduce(w, b1, imax);
             b2 = w3_col_reduce(w, b2, imax);
-            v_lo = lc[(b1 & 0xff) * W3_COLS];
-            v_hi = lc[(b2 & 0xff) * W3_COLS];
+            v_lo = lcw[b1 & 0xff];
+            v_hi = lcw[b2 & 0xff];
             rescue = j2 >= m;             // rank khi above the window: every rank is <= j2 then, so v_hi is the
             thr = v_hi;                   // window's largest value, the threshold of the rescue scan
             __syncwarp(w.cmask);          // the list may be overwritten by the next selection
@@ -265,14 +299,14 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             // crowded window (rare): its value range decides between "all one value" and a finer re-keying
             uint32_t kmin = 0xffffffffu, kmax = 0u;
 #pragma unroll
-            for (int q = 0; q < W3_NKW; ++q) {
-#pragma unroll
-                for (int b = 0; b < 4; ++b) {
-                    if (fl[q] & (0x80u << (8 * b))) {
-                        const uint32_t kx = okey(x[4 * q + b]);
-                        kmin = kx < kmin ? kx : kmin;
-                        kmax = kx > kmax ? kx : kmax;
-                    }
+            for (int h = 0; h < 2; ++h) {
+                unsigned bits = wm[h];
+                while (bits) {
+                    const int pos = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const uint32_t kx = okey(w3_value(src0, src1, 32 * h + pos));
+                    kmin = kx < kmin ? kx : kmin;
+                    kmax = kx > kmax ? kx : kmax;
                 }
             }
             kmin = w3_col_reduce(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
@@ -289,7 +323,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             } else if (!Key::make(a, b, sc)) {
                 return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
             } else {
-                w3_build_keys<Tr, false, FULL, true>(x, kw, w.N, w.part, a, b, sc);
+                w3_build_keys<Tr, false, FULL, true, false>(nullptr, src0, src1, kw, w.N, w.part, a, b, sc);
                 refined = true;
                 continue;
             }
@@ -301,7 +335,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
 #pragma unroll
                 for (int b = 0; b < 4; ++b) {
                     const bool valid = ((kw[q] >> (8 * b)) & 0xffu) != 127u;
-                    const in_t xv = x[4 * q + b];
+                    const in_t xv = w3_value(src0, src1, 4 * q + b);
                     if (valid && xv > thr) { const uint32_t kx = okey(xv); best = kx < best ? kx : best; }
                 }
             }
@@ -315,26 +349,27 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
 
 struct W3Smem {
     // offsets in bytes from the 1024-aligned base
-    size_t tile, list, part, mine, theirs, xst, qr, wq, wi, ww, maskw, misc, keep, bar, total;
+    size_t tile, list, c1, theirs, xflag, lflag, qr, wq, wi, ww, maskw, patch, misc, keep, bar, total;
 };
 __host__ __device__ inline W3Smem w3_smem_layout(size_t vs) {
     W3Smem s{};
     size_t off = 0;
     auto take = [&](size_t bytes, size_t align) { off = (off + align - 1) & ~(align - 1); const size_t at = off; off += bytes; return at; };
     s.tile = take(2 * W3_BOX_BYTES, 1024);
-    s.list = take((size_t)W3_CAP * W3_COLS * 4, 16);
-    s.part = take((size_t)8 * W3_ROWS * vs, 16);          // [8 warps][256 rows] partial risks
-    s.mine = take((size_t)2 * W3_ROWS * vs, 16);          // [parity][row]: this CTA's 64-column partial
-    s.theirs = take((size_t)2 * W3_ROWS * vs, 16);        // written by the peer CTA
-    s.xst = take(4 * sizeof(int), 16);                    // [parity] peer's status word, [2 + parity] unused
+    s.list = take((size_t)W3_COLS * W3_LSTRIDE * 4, 16);
+    s.c1 = take((size_t)W3_COLS * vs, 16);                // first-pass centre of the CTA's columns
+    s.theirs = take((size_t)2 * W3_ROWS * vs, 16);        // [parity][row]: the peer CTA's 64-column partial risks
+    s.xflag = take(2 * 8 * 4, 16);                        // [parity][warp]: the peer's input-range flags
+    s.lflag = take(2 * 8 * 4, 16);                        // [parity][warp]: this CTA's
     s.qr = take((size_t)W3_ROWS * vs, 16);
     s.wq = take((size_t)W2_RCAP * vs, 16);
     s.wi = take((size_t)W2_RCAP * 4, 16);
     s.ww = take(64, 16);
     s.maskw = take(16 * 4, 16);
-    s.misc = take(16, 16);                                // stw, sel
+    s.patch = take(W3_ROWS, 16);                          // [part][value]: 0x7f where the row is dropped
+    s.misc = take(16, 16);                                // stw[2], sel
     s.keep = take(W3_ROWS, 16);
-    s.bar = take(16, 16);
+    s.bar = take(32, 16);                                 // full, empty, xbar[2]
     s.total = off;
     return s;
 }
@@ -356,21 +391,24 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
 
     in_t *tile_s = reinterpret_cast<in_t *>(smem_raw + S.tile);
     in_t *list = reinterpret_cast<in_t *>(smem_raw + S.list);
-    acc_t *part_s = reinterpret_cast<acc_t *>(smem_raw + S.part);
-    acc_t *mine_s = reinterpret_cast<acc_t *>(smem_raw + S.mine);
+    val_t *c1_s = reinterpret_cast<val_t *>(smem_raw + S.c1);
     acc_t *theirs_s = reinterpret_cast<acc_t *>(smem_raw + S.theirs);
-    int *xst_s = reinterpret_cast<int *>(smem_raw + S.xst);
+    uint32_t *xflag_s = reinterpret_cast<uint32_t *>(smem_raw + S.xflag);
+    uint32_t *lflag_s = reinterpret_cast<uint32_t *>(smem_raw + S.lflag);
     acc_t *qr_s = reinterpret_cast<acc_t *>(smem_raw + S.qr);
     acc_t *wq = reinterpret_cast<acc_t *>(smem_raw + S.wq);
     int *wi = reinterpret_cast<int *>(smem_raw + S.wi);
     unsigned *ww = reinterpret_cast<unsigned *>(smem_raw + S.ww);
     uint32_t *maskw = reinterpret_cast<uint32_t *>(smem_raw + S.maskw);
-    int *stw_s = reinterpret_cast<int *>(smem_raw + S.misc);
-    int *sel_s = stw_s + 1;
+    uint8_t *patch_s = smem_raw + S.patch;
+    int *stw_s = reinterpret_cast<int *>(smem_raw + S.misc);        // [2] by round parity
+    int *sel_s = stw_s + 2;
     uint8_t *keep_s = smem_raw + S.keep;
-    u64 *bar = reinterpret_cast<u64 *>(smem_raw + S.bar);
+    u64 *full_bar = reinterpret_cast<u64 *>(smem_raw + S.bar);
+    u64 *empty_bar = full_bar + 1;
+    u64 *xbar = full_bar + 2;                                        // [2] by round parity
 
-    // this thread's unit: column c of the CTA's 64, rows 8k + 2*part + {0, 1}
+    // this thread's column unit: column c of the CTA's 64, rows 8k + 2*part + {0, 1}
     const int cc = lane & 7;
     W3Ctx w;
     w.N = N;
@@ -380,182 +418,184 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     const int part = w.part;
     const int c = warp * 8 + cc;                  // column within the CTA
     const int gc = (int)rank * W3_COLS + c;       // column within the round
-    in_t *lc = list + c;
-    // landing-buffer addresses of this thread's two row phases (128-byte swizzle: the 16-byte chunk index of a row
-    // is XOR-ed with the row number mod 8, which is 2*part / 2*part + 1 for every row this thread reads)
+    in_t *lcw = list + c * W3_LSTRIDE;
+    // tile addresses of this thread's two row phases (128-byte swizzle: the 16-byte chunk index of a row is XOR-ed
+    // with the row number mod 8, which is 2*part / 2*part + 1 for every row this thread reads)
     const int c32 = c & 31;
-    const in_t *src0 = tile_s + (c >> 5) * (W3_BOX_BYTES / 4) + (2 * part) * 32 + ((((c32 >> 2) ^ (2 * part)) << 2) | (c32 & 3));
-    const in_t *src1 = tile_s + (c >> 5) * (W3_BOX_BYTES / 4) + (2 * part + 1) * 32 + ((((c32 >> 2) ^ (2 * part + 1)) << 2) | (c32 & 3));
+    const in_t *src0 = tile_s + (c >> 5) * W3_BOX_WORDS + (2 * part) * 32 + ((((c32 >> 2) ^ (2 * part)) << 2) | (c32 & 3));
+    const in_t *src1 = tile_s + (c >> 5) * W3_BOX_WORDS + (2 * part + 1) * 32 + ((((c32 >> 2) ^ (2 * part + 1)) << 2) | (c32 & 3));
+    // this thread's row unit in the risk sweep: 4-column chunk rh of row 16*t + rg (t = 0..15); after the shuffle
+    // tree the thread holds the total of row 16*rh + rg
+    const int rh = lane & 15, rg = warp * 2 + (lane >> 4);
+    const in_t *rsrc = tile_s + (rh >> 3) * W3_BOX_WORDS + rg * 32 + (((rh & 7) ^ (rg & 7)) << 2);
+    const int my_row = 16 * rh + rg;
 
     const uint32_t tile_bytes = 2 * W3_BOX_BYTES;
+    constexpr uint32_t XBYTES = W3_ROWS * sizeof(acc_t) + (Tr::fixed ? 8 * 4 : 0);
     if (tid == 0) {
         if (smem_u32(tile_s) & 1023u) __trap();      // the swizzle pattern is a function of the address bits
-        mbar_init(bar, 1);
-        if (cluster_id < p.T) {
-            mbar_expect_tx(bar, tile_bytes);
-            const int row0 = (int)(cluster_id * p.N);
-            tma_load_box(tile_s, &tmap, (int)rank * W3_COLS, row0, bar);
-            tma_load_box(tile_s + W3_BOX_BYTES / 4, &tmap, (int)rank * W3_COLS + 32, row0, bar);
-        }
+        mbar_init(full_bar, 1);
+        mbar_init(empty_bar, W3_THREADS);
+        mbar_init(xbar, 1);
+        mbar_init(xbar + 1, 1);
+        stw_s[0] = STW_OK;
+        mbar_expect_tx(full_bar, tile_bytes);
+        const int row0 = (int)(cluster_id * p.N);
+        tma_load_box(tile_s, &tmap, (int)rank * W3_COLS, row0, full_bar);
+        tma_load_box(tile_s + W3_BOX_WORDS, &tmap, (int)rank * W3_COLS + 32, row0, full_bar);
     }
     __syncthreads();
-    // the peer must be running before anything is written into its shared memory
+    // the peer must be running (its barriers initialised) before anything is sent into its shared memory
     cluster_sync_all();
 
     const bool shape2 = second_pass_shape_panic(p);
     const bool high = p.tie == SVOC_TIE_HIGH_INDEX_KEPT;
     const uint32_t theirs_remote = map_to_peer(smem_u32(theirs_s), peer);
-    const uint32_t xst_remote = map_to_peer(smem_u32(xst_s), peer);
+    const uint32_t xflag_remote = map_to_peer(smem_u32(xflag_s), peer);
+    const uint32_t xbar_remote = map_to_peer(smem_u32(xbar), peer);
 
     uint32_t it = 0;
     for (i64 r = cluster_id; r < p.T; r += n_clusters, ++it) {
         const uint32_t par = it & 1u;
+        const bool has_next = r + n_clusters < p.T;
         const in_t *gcol = reinterpret_cast<const in_t *>(p.pred) + (size_t)r * p.N * W3_D + gc;
-        if (tid == 0) *stw_s = STW_OK;
-        // ---- phase 0: the round's values into registers
-        mbar_wait(bar, par);
-        in_t x[W3_NV];
-#pragma unroll
-        for (int k = 0; k < W3_NV / 2; ++k) {
-            x[2 * k] = src0[k * 256];             // 8 rows of 32 words
-            x[2 * k + 1] = src1[k * 256];
+        if (tid == 0) {
+            stw_s[par ^ 1u] = STW_OK;                              // the next round's status word
+            mbar_expect_tx(xbar + par, XBYTES);                    // this round's exchange
+            if (has_next) {                                        // pull the next round towards L2 meanwhile
+                const int row0 = (int)((r + n_clusters) * p.N);
+                tma_prefetch_box(&tmap, (int)rank * W3_COLS, row0);
+                tma_prefetch_box(&tmap, (int)rank * W3_COLS + 32, row0);
+            }
         }
-        // ---- phase 1a: key scale from a 64-row sample (rows 0..63: the first 16 values of every part) and the keys
+        // ---- phase 1a: the tile has landed; key scale from a 64-row sample (rows 0..63: the first 16 values of
+        //      every part), then the keys
+        mbar_wait(full_bar, par);
         bool col_const = false, col_fb = false, refined1 = false;
         in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
         typename Key::Scale sc{};
+        unsigned kw[W3_NKW];
+        {
+            in_t x[W3_NV];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            lo = vmin(lo, x[j]);
-            hi = vmax(hi, x[j]);
-        }
-        lo = w3_col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
-        hi = w3_col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
-        if (!(hi > lo)) {                         // degenerate sample: exact sweep, which also detects a constant column
+            for (int k = 0; k < W3_NV / 2; ++k) {
+                x[2 * k] = src0[k * 256];             // 8 rows of 32 words
+                x[2 * k + 1] = src1[k * 256];
+            }
 #pragma unroll
-            for (int j = 0; j < W3_NV; ++j) {
-                if (FULL || w3_row(j, part) < N) {
-                    lo = vmin(lo, x[j]);
-                    hi = vmax(hi, x[j]);
-                }
+            for (int j = 0; j < 16; ++j) {
+                lo = vmin(lo, x[j]);
+                hi = vmax(hi, x[j]);
             }
             lo = w3_col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
             hi = w3_col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
-        }
-        col_const = !(hi > lo);
-        col_fb = !col_const && !Key::make(lo, hi, sc);
-        if (col_fb) {
-            // No keys will be built, so nothing below has read values 16..63 yet.  They must have ARRIVED in their
-            // registers before the barrier that hands the landing buffer to the next copy: fold them into a word
-            // the compiler has to produce (the store never happens).
-            uint32_t fold = 0;
+            if (!(hi > lo)) {                         // degenerate sample: exact sweep, which also detects a constant column
 #pragma unroll
-            for (int j = 16; j < W3_NV; ++j) fold ^= okey(x[j]);
-            if (fold == 0x9e3779b9u && p.T < 0) *sel_s = (int)fold;
-        }
-        unsigned kw[W3_NKW];
+                for (int j = 0; j < W3_NV; ++j) {
+                    if (FULL || w3_row(j, part) < N) {
+                        lo = vmin(lo, x[j]);
+                        hi = vmax(hi, x[j]);
+                    }
+                }
+                lo = w3_col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+                hi = w3_col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+            }
+            col_const = !(hi > lo);
+            col_fb = !col_const && !Key::make(lo, hi, sc);
 #pragma unroll
-        for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
-        if (!col_const && !col_fb) w3_build_keys<Tr, true, FULL, false>(x, kw, N, part, lo, hi, sc);
-        // every value has been consumed: the landing buffer is free for the next round, whose copy now has the
-        // whole of this round's computation to arrive
-        __syncthreads();
-        if (tid == 0 && r + n_clusters < p.T) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_expect_tx(bar, tile_bytes);
-            const int row0 = (int)((r + n_clusters) * p.N);
-            tma_load_box(tile_s, &tmap, (int)rank * W3_COLS, row0, bar);
-            tma_load_box(tile_s + W3_BOX_BYTES / 4, &tmap, (int)rank * W3_COLS + 32, row0, bar);
+            for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
+            if (!col_const && !col_fb) w3_build_keys<Tr, true, FULL, false, true>(x, src0, src1, kw, N, part, lo, hi, sc);
         }
-        // ---- the two passes share ONE inlined copy of the centre code (the kernel is 250 KB of SASS otherwise):
-        //      pass 0 = first-pass centre, risks, row selection, key patching; pass 1 = second-pass centre
-        val_t e1 = 0;
+        // ---- the two passes share ONE inlined copy of the centre code: pass 0 = first-pass centre, risks, row
+        //      selection, key patching; pass 1 = second-pass centre
 #pragma unroll 1
         for (int pass = 0;; ++pass) {
             bool refined = false;
-            const val_t ctr = w3_centre<Tr, FULL>(w, x, kw, gcol, pass ? keep_s : nullptr, pass ? R : N,
-                                                  pass ? p.centre2 : p.centre, col_const, col_fb, lo, lc, refined);
+            const val_t ctr = w3_centre<Tr, FULL>(w, src0, src1, kw, gcol, pass ? keep_s : nullptr, pass ? R : N,
+                                                  pass ? p.centre2 : p.centre, col_const, col_fb, lo, lcw, refined);
             if (pass) {
                 if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = ctr;
                 break;
             }
-            e1 = ctr;
             refined1 = refined;
-            if (part == 0 && p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * W3_D + gc] = e1;
+            if (part == 0) {
+                c1_s[c] = ctr;
+                if (p.essence1) reinterpret_cast<val_t *>(p.essence1)[(size_t)r * W3_D + gc] = ctr;
+            }
+            __syncthreads();
 
-        // ---- phase 2: quadratic risk.  A thread holds (x - e1)^2 of 64 rows of ONE column; the 8 columns of the
-        //      warp are folded with a transposing shuffle tree (lane bit 0 keeps the rows of its own parity, bits 1
-        //      and 2 the next two row-index bits), 8 values at a time, which leaves every lane with 8 row sums over
-        //      the warp's columns; warp partials meet in shared memory, summed in a fixed order.
-        {
-            const bool b0 = cc & 1, b1 = cc & 2, b2 = cc & 4;
-            bool bad = false;
+            // ---- phase 2: quadratic risk.  Row-wise sweep of the tile: 16 lanes share a row (a quarter-warp reads
+            //      one 128-byte line), a thread visits rows 16t + rg, t = 0..15, and folds (x - e1)^2 over its four
+            //      columns; the 16 partials of a thread and the 16 lanes of a row are then folded together by a
+            //      transposing shuffle tree (xor 8, 4, 2, 1: fixed order), which leaves every thread with the total
+            //      of ONE row over the CTA's 64 columns.
+            acc_t own;
+            {
+                val_t e4[4];
 #pragma unroll
-            for (int n = 0; n < 8; ++n) {          // values 8n .. 8n+7: rows 32n + 8*(0..3) + 2*part + {0,1}
-                acc_t u[4];
+                for (int k = 0; k < 4; ++k) e4[k] = c1_s[4 * rh + k];
+                acc_t v[16];
+                bool bad = false;
+#pragma unroll
+                for (int t = 0; t < 16; ++t) {
+                    const int4 raw = *reinterpret_cast<const int4 *>(rsrc + t * 16 * 32);
+                    in_t xr[4];
+                    memcpy(xr, &raw, 16);
+                    acc_t q = 0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        if constexpr (Tr::fixed) {
+                            const bool out = p.constrained ? ((xr[k] < 0) | ((i64)xr[k] > WSAD))
+                                                           : (((i64)xr[k] > ENGINE_RANGE) | ((i64)xr[k] < -ENGINE_RANGE));
+                            bad |= out & (FULL || 16 * t + rg < N);
+                        }
+                        q += Tr::dev(xr[k], e4[k]);
+                    }
+                    v[t] = q;
+                }
+                const bool b3 = rh & 8, b2 = rh & 4, b1 = rh & 2, b0 = rh & 1;
+                acc_t u8[8], u4[4], u2[2];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {          // keep t = i + 8*b3
+                    const acc_t keep = b3 ? v[i + 8] : v[i], send = b3 ? v[i] : v[i + 8];
+                    u8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const in_t xa = x[8 * n + 2 * i], xb = x[8 * n + 2 * i + 1];
-                    if constexpr (Tr::fixed) {
-                        bool ba, bb;
-                        if (p.constrained) {
-                            ba = (xa < 0) | ((i64)xa > WSAD);
-                            bb = (xb < 0) | ((i64)xb > WSAD);
-                        } else {
-                            ba = ((i64)xa > ENGINE_RANGE) | ((i64)xa < -ENGINE_RANGE);
-                            bb = ((i64)xb > ENGINE_RANGE) | ((i64)xb < -ENGINE_RANGE);
-                        }
-                        if (!FULL) {
-                            ba &= w3_row(8 * n + 2 * i, part) < N;
-                            bb &= w3_row(8 * n + 2 * i + 1, part) < N;
-                        }
-                        bad |= ba | bb;
-                    }
-                    const acc_t da = Tr::dev(xa, e1), db = Tr::dev(xb, e1);
-                    const acc_t keep = b0 ? db : da, send = b0 ? da : db;
-                    u[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                    const acc_t keep = b2 ? u8[i + 4] : u8[i], send = b2 ? u8[i] : u8[i + 4];
+                    u4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
                 }
-                acc_t t[2];
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
-                    const acc_t keep = b1 ? u[2 * i + 1] : u[2 * i], send = b1 ? u[2 * i] : u[2 * i + 1];
-                    t[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                    const acc_t keep = b1 ? u4[i + 2] : u4[i], send = b1 ? u4[i] : u4[i + 2];
+                    u2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
                 }
-                const acc_t keep = b2 ? t[1] : t[0], send = b2 ? t[0] : t[1];
-                const acc_t s = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                // this lane's row: value index j = 8n + 4*b2 + 2*b1 + b0
-                const int row = 32 * n + 8 * ((b2 ? 2 : 0) + (b1 ? 1 : 0)) + 2 * part + (b0 ? 1 : 0);
-                part_s[warp * W3_ROWS + row] = s;
+                {
+                    const acc_t keep = b0 ? u2[1] : u2[0], send = b0 ? u2[0] : u2[1];
+                    own = keep + __shfl_xor_sync(0xffffffffu, send, 1);        // row 16*rh + rg
+                }
+                // to the peer: this row's partial (and, fixed form, the warp's input-range flag)
+                st_async_peer(theirs_remote + (uint32_t)((par * W3_ROWS + my_row) * sizeof(acc_t)), own, xbar_remote + par * 8u);
+                if constexpr (Tr::fixed) {
+                    const uint32_t anybad = __any_sync(0xffffffffu, bad) ? 1u : 0u;
+                    if (lane == 0) {
+                        lflag_s[par * 8 + warp] = anybad;
+                        st_async_peer(xflag_remote + (par * 8 + warp) * 4u, anybad, xbar_remote + par * 8u);
+                    }
+                }
             }
-            if (bad) atomicMin(stw_s, p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE);
-        }
-        __syncthreads();
-        {
-            // this CTA's 64-column partial of row `tid`, to both CTAs of the pair
-            acc_t q = part_s[tid];
-#pragma unroll
-            for (int k = 1; k < 8; ++k) q += part_s[k * W3_ROWS + tid];
-            mine_s[par * W3_ROWS + tid] = q;
-            st_peer(theirs_remote + (uint32_t)((par * W3_ROWS + tid) * sizeof(acc_t)), q);
-            if (tid == 0) st_peer(xst_remote + par * 4u, *stw_s);
-        }
-        cluster_sync_all();
-        {
-            const acc_t a = mine_s[par * W3_ROWS + tid], b = theirs_s[par * W3_ROWS + tid];
-            const acc_t q = rank == 0 ? a + b : b + a;        // partial(rank 0) + partial(rank 1) on both CTAs
-            qr_s[tid] = q;
-            if (rank == 0 && p.qr && tid < N) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * p.N + tid] = q;
-            if (tid == 0) {
-                const int other = xst_s[par];
-                if (other != STW_OK) atomicMin(stw_s, other);
+            mbar_wait(xbar + par, (it >> 1) & 1u);
+            {
+                const acc_t other = theirs_s[par * W3_ROWS + my_row];
+                const acc_t q = rank == 0 ? own + other : other + own;        // partial(rank 0) + partial(rank 1) on both CTAs
+                qr_s[my_row] = q;
+                if (rank == 0 && p.qr && my_row < N) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * p.N + my_row] = q;
             }
-        }
-        __syncthreads();
+            __syncthreads();
 
-        // ---- phase 3: which rows are kept — warp 0 (w2_select_rows) while warp 1 does the first-pass reliability;
-        //      exact all-pairs ranking when the selection gives up on this round's risks.  Both CTAs of the pair
-        //      compute the same thing from the same risks; rank 0 writes the per-round outputs.
-        {
+            // ---- phase 3: which rows are kept — warp 0 (w2_select_rows) while warp 1 does the first-pass reliability;
+            //      exact all-pairs ranking when the selection gives up on this round's risks.  Both CTAs of the pair
+            //      compute the same thing from the same risks; rank 0 writes the per-round outputs.
             constexpr int NS = W3_ROWS / 32;
             if (warp == 0) {
                 unsigned words[NS];
@@ -568,12 +608,6 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
 #pragma unroll
                     for (int j = 0; j < NS; ++j) mw = lane == j ? words[j] : mw;
                     if (lane < NS) maskw[lane] = mw;
-                    __syncwarp();
-                    // keep flags as bytes for the exact fallbacks: bit b of a mask byte -> byte b (0 / 1)
-                    const unsigned bits8 = (maskw[lane >> 2] >> (8 * (lane & 3))) & 0xffu;
-                    const unsigned lo4 = ((bits8 & 0xfu) * 0x00204081u) & 0x01010101u;
-                    const unsigned hi4 = ((bits8 >> 4) * 0x00204081u) & 0x01010101u;
-                    *reinterpret_cast<uint2 *>(keep_s + 8 * lane) = make_uint2(lo4, hi4);
                 }
                 if (lane == 0) *sel_s = fast ? 1 : 0;
             } else if (warp == 1) {
@@ -585,6 +619,10 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                 if (lane == 0) {
                     int stw = STW_OK;
                     if constexpr (Tr::fixed) {
+                        uint32_t anybad = 0;
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) anybad |= lflag_s[par * 8 + k] | xflag_s[par * 8 + k];
+                        if (anybad) stw = p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE;
                         const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
                         if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
                         if (rank == 0) reinterpret_cast<i64 *>(p.rel1)[r] = rel1;
@@ -593,7 +631,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                         if (!(rel1 >= 0 && rel1 <= 1)) stw = min(stw, STW_REL1_RANGE);
                         if (rank == 0) reinterpret_cast<val_t *>(p.rel1)[r] = rel1;
                     }
-                    if (stw != STW_OK) atomicMin(stw_s, stw);
+                    if (stw != STW_OK) atomicMin(stw_s + par, stw);
                 }
             }
             __syncthreads();
@@ -605,11 +643,16 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                     const acc_t q = qr_s[j];
                     rk += (q < mineq) | ((q == mineq) & (high ? j > tid : j < tid));
                 }
-                const bool kept = tid < N && rk < R;
-                keep_s[tid] = kept ? 1 : 0;
-                const unsigned bal = __ballot_sync(0xffffffffu, kept);
+                const unsigned bal = __ballot_sync(0xffffffffu, tid < N && rk < R);
                 if (lane == 0) maskw[warp] = bal;
                 __syncthreads();
+            }
+            // every thread turns the mask bit of row `tid` into the byte forms the column units read: keep_s[row]
+            // (0 / 1, exact fallbacks) and patch_s[part][value] (0x7f where dropped: OR-ed into the keys)
+            {
+                const bool kept = (maskw[tid >> 5] >> (tid & 31)) & 1u;
+                keep_s[tid] = kept ? 1 : 0;
+                patch_s[((tid >> 1) & 3) * W3_NV + 2 * (tid >> 3) + (tid & 1)] = kept ? 0 : 0x7f;
             }
             // second-pass reliability, mask and status
             if (warp == 0) {
@@ -638,39 +681,49 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                         }
                         if (rank == 0) reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
                     }
-                    if (stw != STW_OK) atomicMin(stw_s, stw);
+                    if (stw != STW_OK) atomicMin(stw_s + par, stw);
                     if (rank == 0) {         // nothing later contributes to the status
-                        const int sw = *stw_s;
+                        const int sw = stw_s[par];
                         p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
                     }
                 }
             }
-        }
-        // ---- phase 4 set-up: keys of the kept rows only; the loop then runs the second-pass centre
+            __syncthreads();                 // keep_s / patch_s are complete
+            // ---- phase 4 set-up: keys of the kept rows only; the loop then runs the second-pass centre
             if (shape2) {
                 if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = 0;
                 break;
             }
             if (!col_const && !col_fb) {
                 if (refined1) {
-                    // the first pass re-keyed the column: back to the first-pass scale, dropped rows -> sentinel
+                    // the first pass re-keyed the column: back to the first-pass scale
 #pragma unroll
                     for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
-                    w3_build_keys<Tr, true, FULL, false>(x, kw, N, part, lo, hi, sc);
+                    w3_build_keys<Tr, true, FULL, false, false>(nullptr, src0, src1, kw, N, part, lo, hi, sc);
                 }
-                // dropped rows of this thread -> sentinel key.  Key word q holds rows 32*(q>>1) + 16*(q&1) +
-                // {0, 1, 8, 9} + 2*part: two bit pairs of mask word q>>1, spread to four bytes by one multiply
+                // dropped rows -> sentinel key (keys are <= 127, so OR-ing 0x7f gives 127)
 #pragma unroll
-                for (int g = 0; g < W3_NKW / 2; ++g) {
-                    const unsigned drop = ~maskw[g] >> (2 * part);
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const unsigned t = drop >> (16 * h);
-                        const unsigned nib = (t & 3u) | ((t >> 6) & 0xcu);
-                        kw[2 * g + h] |= ((nib * 0x00204081u) & 0x01010101u) * 0x7fu;
-                    }
+                for (int q4 = 0; q4 < W3_NKW / 4; ++q4) {
+                    const uint4 d = *reinterpret_cast<const uint4 *>(patch_s + part * W3_NV + 16 * q4);
+                    kw[4 * q4] |= d.x; kw[4 * q4 + 1] |= d.y; kw[4 * q4 + 2] |= d.z; kw[4 * q4 + 3] |= d.w;
                 }
             }
+        }
+        // ---- this thread has made its last read of the tile; once all have, the next round is copied in.  The WHOLE
+        //      warp 0 waits: were lane 0 alone to spin here while its 31 siblings spin on the full barrier at the top
+        //      of the next round — which only lane 0's copy can complete — the warp would depend on the hardware
+        //      switching between its two divergent spin loops (it hung, rarely: whenever another warp was last).
+        mbar_arrive(empty_bar);
+        if (warp == 0 && has_next) {
+            mbar_wait(empty_bar, par);
+            if (lane == 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(full_bar, tile_bytes);
+                const int row0 = (int)((r + n_clusters) * p.N);
+                tma_load_box(tile_s, &tmap, (int)rank * W3_COLS, row0, full_bar);
+                tma_load_box(tile_s + W3_BOX_WORDS, &tmap, (int)rank * W3_COLS + 32, row0, full_bar);
+            }
+            __syncwarp();
         }
     }
 }

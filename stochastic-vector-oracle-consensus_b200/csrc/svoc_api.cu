@@ -260,6 +260,7 @@ int montecarlo_device(const svoc_config *cfg, const svoc_gen_config *gen, int64_
     if (gen->n_oracles != cfg->n_oracles || gen->dimension != cfg->dimension || gen->n_failing != cfg->n_failing)
         return fail("consensus and generator configurations disagree on the shape");
     if (gen->n_params < 1 || gen->n_params > SVOC_MAX_LAW_PARAMS) return fail("n_params out of range");
+    if (gen->failing_prob != 0.0) return fail("the fused Monte-Carlo kernel draws exactly n_failing failing oracles; use svoc_generate for failing_prob");
     if (cfg->centre < 0 || cfg->centre > 2 || cfg->centre2 < -1 || cfg->centre2 > 2 || cfg->tie_rule < 0 || cfg->tie_rule > 1)
         return fail("bad centre / tie rule");
     if ((i64)cfg->n_oracles * cfg->dimension >= 0xFFFF0000LL) return fail("n_oracles * dimension too large");

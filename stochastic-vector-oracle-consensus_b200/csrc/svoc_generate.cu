@@ -43,7 +43,8 @@ __global__ void __launch_bounds__(256) generate_kernel(const GenParams p) {
         const uint32_t mine = kk[i];
         int rank = 0;
         for (int j = 0; j < N; ++j) rank += (kk[j] < mine || (kk[j] == mine && j < i)) ? 1 : 0;
-        failing[w] = rank < F ? 1 : 0;
+        // Bernoulli mode: the position key itself is the oracle's uniform draw
+        failing[w] = p.c.failing_prob > 0.0 ? (u01(mine) < (float)p.c.failing_prob ? 1 : 0) : (rank < F ? 1 : 0);
     }
     __syncthreads();
     if (p.honest) {
@@ -75,6 +76,7 @@ extern "C" int svoc_generate(const svoc_gen_config *cfg, int64_t n_rounds, void 
     if (!pred) return fail("null prediction buffer");
     if (cfg->n_oracles < 1 || cfg->dimension < 1 || cfg->n_oracles > 65535) return fail("bad generator shape");
     if (cfg->n_failing < 0 || cfg->n_failing > cfg->n_oracles) return fail("n_failing out of range");
+    if (!(cfg->failing_prob >= 0.0 && cfg->failing_prob <= 1.0)) return fail("failing_prob must lie in [0, 1]");
     if (cfg->n_params < 1 || cfg->n_params > SVOC_MAX_LAW_PARAMS) return fail("n_params out of range");
     if (cfg->law < SVOC_LAW_BETA || cfg->law > SVOC_LAW_ARCTAN_GAUSSIAN) return fail("unknown law");
     if ((i64)cfg->n_oracles * cfg->dimension >= 0xFFFF0000LL) return fail("n_oracles * dimension too large");

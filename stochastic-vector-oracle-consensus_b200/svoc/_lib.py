@@ -49,7 +49,7 @@ class SvocGenConfig(C.Structure):
         ("n_oracles", C.c_int32), ("dimension", C.c_int32), ("n_failing", C.c_int32), ("law", C.c_int32),
         ("failing", C.c_int32), ("dtype", C.c_int32), ("n_params", C.c_int32), ("reserved", C.c_int32),
         ("a", C.c_double * 8), ("b", C.c_double * 8), ("shift", C.c_double), ("seed", C.c_uint64),
-        ("trial_offset", C.c_int64),
+        ("trial_offset", C.c_int64), ("failing_prob", C.c_double),
     ]
 
 

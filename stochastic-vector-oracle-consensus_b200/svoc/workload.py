@@ -39,7 +39,7 @@ def _seq(v, n=8):
     return v
 
 
-def _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype) -> SvocGenConfig:
+def _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype, failing_prob=0.0) -> SvocGenConfig:
     av, bv = _seq(a), _seq(b)
     if len(av) != len(bv):
         raise ValueError("a and b need the same length")
@@ -48,15 +48,18 @@ def _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed
                              "arctan_gaussian": _lib.LAW_ARCTAN_GAUSSIAN}[law],
                         failing={"uniform": _lib.FAIL_UNIFORM, "colluding": _lib.FAIL_COLLUDING}[failing],
                         dtype=_DTYPES[dtype], n_params=len(av), reserved=0, shift=float(shift),
-                        seed=int(seed) & (2**64 - 1), trial_offset=int(trial_offset))
+                        seed=int(seed) & (2**64 - 1), trial_offset=int(trial_offset), failing_prob=float(failing_prob))
     for k, (x, y) in enumerate(zip(av, bv)):
         cfg.a[k], cfg.b[k] = float(x), float(y)
     return cfg
 
 
 def generate(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="beta", failing="uniform", shift=0.15,
-             seed=0, trial_offset=0, dtype=torch.float32, device=None) -> Generated:
+             seed=0, trial_offset=0, dtype=torch.float32, device=None, failing_prob=0.0) -> Generated:
     """Draw `n_rounds` rounds of oracle predictions on the device.
+
+    failing_prob > 0 switches from "exactly n_failing failing oracles" to "every oracle fails independently
+    with that probability" (the failing-fraction sweep of BASELINE config 2).
 
     law="beta": honest ~ beta(a[d], b[d]), failing ~ uniform(0, 1); law="gaussian": honest ~
     normal(mu=a[d], sigma=b[d]), failing ~ uniform(mu, 5 sigma).  failing="colluding" makes every
@@ -66,7 +69,7 @@ def generate(n_rounds, n_oracles, dimension, n_failing, a=10.0, b=10.0, law="bet
     device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     if device.type != "cuda":
         raise ValueError("svoc.generate runs on a CUDA device only")
-    cfg = _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype)
+    cfg = _gen_config(n_oracles, dimension, n_failing, a, b, law, failing, shift, seed, trial_offset, dtype, failing_prob)
     pred = torch.empty((n_rounds, n_oracles, dimension), dtype=dtype, device=device)
     words = torch.empty((n_rounds, (n_oracles + 31) // 32), dtype=torch.int32, device=device)
     if n_rounds:
@@ -128,9 +131,9 @@ class RunningStats:
         """SUM the local accumulators over all ranks (NCCL over NVLink on GPUs); returns (counts, sums)
         of the whole job and leaves the local accumulators untouched."""
         from .distributed import allreduce_stats
-        c, s = allreduce_stats(self.counts, self.sums, group)
-        self._reduced = (c, s)
-        return c, s
+        # the reduced copies are allocated once and reused by every later call
+        self._reduced = allreduce_stats(self.counts, self.sums, group, out=self._reduced)
+        return self._reduced
 
     def summary(self, reduced: bool = False) -> dict:
         c, s = self._reduced if (reduced and self._reduced is not None) else (self.counts, self.sums)

@@ -104,7 +104,7 @@ def main():
     # ---- the reference's Monte-Carlo benchmark at large K (statistical anchor for the
     #      on-device generator + engine; the published K=300 table is in BASELINE.md)
     stats = []
-    for (n, f) in [(7, 2), (20, 2), (20, 15)]:
+    for (n, f) in [(7, 2), (20, 2), (20, 15), (7, 0), (7, 1)]:      # F = 0, 1: anchors of the failing-fraction sweep (config 2)
         for a in (10, 20, 30, 100):
             np.random.seed(1000 * n + 10 * f + a)
             buf = io.StringIO()

@@ -206,14 +206,23 @@ def test_row_selection_matches_all_pairs_ranking(kind, N, D):
     rng = np.random.default_rng(seed_of(kind, N, D))
     T = 24
     x = _selection_inputs(kind, T, N, D, rng)
+    idx = torch.arange(N, device="cuda")
     for F in (0, 1, N // 5, N // 2, N - 33, N - 2):
         for tie in (svoc.TIE_HIGH_INDEX_KEPT, svoc.TIE_LOW_INDEX_KEPT):
             t = torch.from_numpy(x.astype(np.float32)).cuda()
             a = svoc.consensus_float(t, F, tie_rule=tie, want_rank=True)
             b = svoc.consensus_float(t, F, tie_rule=tie, want_rank=False)
-            assert torch.equal(a.reliable_words, b.reliable_words), (kind, F, tie, "f32")
-            assert torch.equal(a.consensus, b.consensus) and torch.equal(a.status, b.status)
-            torch.testing.assert_close(a.rel2, b.rel2, rtol=1e-5, atol=1e-6)
+            # each result against its OWN risks (the two calls may run different kernels, whose fp32 risk sums differ in
+            # the last bit: 'two_values' and 'constant' rounds tie exactly in real arithmetic, so rounding alone orders them)
+            for res in (a, b):
+                q = res.qr
+                before = (q[:, None, :] < q[:, :, None]) | ((q[:, None, :] == q[:, :, None]) & (
+                    (idx[None, None, :] > idx[None, :, None]) if tie == svoc.TIE_HIGH_INDEX_KEPT else (idx[None, None, :] < idx[None, :, None])))
+                assert torch.equal(res.reliable, before.sum(dim=2) < N - F), (kind, F, tie, "f32")
+            assert torch.equal(a.status, b.status)
+            if torch.equal(a.qr, b.qr):
+                assert torch.equal(a.reliable_words, b.reliable_words) and torch.equal(a.consensus, b.consensus)
+                torch.testing.assert_close(a.rel2, b.rel2, rtol=1e-5, atol=1e-6)
             assert torch.all(b.reliable.sum(dim=1) == N - F)
             # fixed-point form on the same rounds: risks are 64-bit integers, selected through their float images
             ti = torch.from_numpy((x * 1e6).astype(np.int32)).cuda()

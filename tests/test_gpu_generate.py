@@ -155,3 +155,28 @@ def test_kumaraswamy_and_arctan_gaussian_laws():
     z = (np.tan(np.pi * (x[h].ravel()[:40000] - 0.5)) - np.tan(np.pi * (e - 0.5))) / sigma     # denormalize, standardise
     assert stats.kstest(z, "norm").pvalue > 1e-3
     assert x.min() > 0 and x.max() < 1
+
+
+def test_bernoulli_failing_mode():
+    """failing_prob > 0: every oracle fails independently with that probability (the failing-fraction sweep of
+    BASELINE config 2) — the number of failing oracles per round is Binomial(N, p), positions are uniform, failing
+    rows are uniform(0, 1), honest rows keep the law; failing_prob = 0 keeps the exact-count mode."""
+    import svoc
+    from scipy import stats
+    T, N, D = 200_000, 7, 2
+    for p in (0.1, 0.4):
+        g = svoc.generate(T, N, D, 2, a=10.0, b=15.0, seed=21, failing_prob=p)
+        h = g.honest.cpu().numpy()
+        k = (~h).sum(axis=1)
+        expect = stats.binom.pmf(np.arange(N + 1), N, p) * T
+        obs = np.bincount(k, minlength=N + 1)
+        assert stats.chisquare(obs[expect > 5], expect[expect > 5] * obs[expect > 5].sum() / expect[expect > 5].sum()).pvalue > 1e-4
+        per_pos = (~h).mean(axis=0)
+        assert np.all(np.abs(per_pos - p) < 5 * np.sqrt(p * (1 - p) / T))
+        x = g.pred.cpu().numpy().astype(np.float64)
+        assert stats.kstest(x[~h].ravel()[:50000], "uniform").pvalue > 1e-4
+        assert stats.kstest(x[h][:, 0][:50000], stats.beta(10, 15).cdf).pvalue > 1e-4
+    g0 = svoc.generate(1000, N, D, 2, a=10.0, b=15.0, seed=21)
+    assert torch.all((~g0.honest).sum(dim=1) == 2)
+    with pytest.raises(RuntimeError):
+        svoc.generate(10, N, D, 2, failing_prob=1.5)

@@ -23,7 +23,7 @@ def test_header_symbols_are_exported_and_bound():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/svoc.h but not exported"
         assert n in _lib.SYMBOLS, f"{n} has no ctypes signature in svoc/_lib.py"
-    assert lib.svoc_version() == 100
+    assert lib.svoc_version() == 101
 
 
 def test_struct_layout_matches_header():
@@ -31,6 +31,7 @@ def test_struct_layout_matches_header():
     assert C.sizeof(_lib.SvocConfig) == 56
     assert C.sizeof(_lib.SvocOutputs) == 10 * 8
     assert _lib.SvocConfig.max_spread_wsad.offset == 16 and _lib.SvocConfig.centre.offset == 32
+    assert C.sizeof(_lib.SvocGenConfig) == 32 + 128 + 32 and _lib.SvocGenConfig.failing_prob.offset == 184
 
 
 def test_argument_errors_without_gpu():
@@ -48,7 +49,7 @@ def test_argument_errors_without_gpu():
     assert lib.svoc_consensus_fixed(C.byref(cfg), None, 0, C.byref(outs), None) == -1  # outputs still required
     assert lib.svoc_kernel_variant(C.byref(cfg)) == b"small8"
     cfg.n_oracles = 256
-    assert lib.svoc_kernel_variant(C.byref(cfg)) in (b"generic", b"wide", b"wide2", b"column")
+    assert lib.svoc_kernel_variant(C.byref(cfg)) in (b"generic", b"wide", b"wide2", b"wide3")
 
 
 def test_product_path_never_imports_the_oracle():
