@@ -44,9 +44,9 @@ constexpr int W3_D = 128;            // columns per round (two CTAs)
 constexpr int W3_ROWS = 256;         // rows of a landing box (rows >= N are ignored)
 constexpr int W3_NV = 64;            // values per thread
 constexpr int W3_NKW = 16;           // packed key words per thread
-constexpr int W3_CAP = 32;           // candidate slots per column
-constexpr int W3_LSTRIDE = 36;       // words per column in the candidate list: 32 slots + 4 sentinels; 36 = 4 mod 32,
-                                     // so the 128-bit reads of the 8 columns of a warp fall into 8 different bank groups
+constexpr int W3_CAP = 16;           // candidate slots per column (one key bucket; fuller buckets are re-keyed)
+constexpr int W3_LSTRIDE = 20;       // words per column in the candidate list: 16 slots + 4 sentinels; 20 * c mod 32 takes
+                                     // 8 different multiples of 4 for the 8 columns of a warp: conflict-free 128-bit reads
 constexpr int W3_BOX_BYTES = 32 * W3_ROWS * 4;     // one 32-column box
 constexpr int W3_BOX_WORDS = W3_BOX_BYTES / 4;
 
@@ -214,118 +214,133 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             if (lt <= klo) { prefix = cand; L = lt; }
             else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
         }
-        // ---- the window: the bucket of rank klo alone when rank khi is inside it, else that and the next two.
-        //      One bit per value: the byte MSBs of a key word are gathered into a nibble by one multiply
-        //      (bits 7, 15, 23, 31 -> 28..31), 16 nibbles make the 64-bit mask of this thread's window rows.
-        const unsigned span = (khi < LE) ? 1u : 3u;
-        const unsigned up = prefix + span > 127u ? 127u : prefix + span;
-        const unsigned c1b = (128u - prefix) * 0x01010101u, c2b = (128u - up) * 0x01010101u;
-        unsigned wm[2] = {0u, 0u};
+        // ---- resolving the bucket.  One bit per value: the byte MSBs of a key word are gathered into a nibble by
+        //      one multiply (bits 7, 15, 23, 31 -> 28..31), 16 nibbles make the 64-bit mask of this thread's rows.
+        //      w1 = rows whose key is `prefix`.
+        const unsigned cA = (128u - prefix) * 0x01010101u;            // byte MSB set <=> key >= prefix
+        const unsigned cB = cA - 0x01010101u;                         //              <=> key >= prefix + 1
+        unsigned w1[2] = {0u, 0u};
 #pragma unroll
         for (int q = 0; q < W3_NKW; ++q) {
-            const unsigned fl = (kw[q] + c1b) & ~(kw[q] + c2b) & 0x80808080u;
-            wm[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
+            const unsigned fl = (kw[q] + cA) & ~(kw[q] + cB) & 0x80808080u;
+            w1[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
         }
-        const int mine = __popc(wm[0]) + __popc(wm[1]);
-        // slot offset of this part = candidates of the lower parts; m = all of them
-        int off = 0, m = 0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int cq = __shfl_sync(w.cmask, mine, w.lane_base + 8 * q);
-            m += cq;
-            if (q < w.part) off += cq;
-        }
-        const int j1 = klo - L, j2 = khi - L;
         bool rescue = false;
         in_t thr = const_value;
-        if (m <= W3_CAP) {
-            // values of this part's window rows -> slots off.., fetched from the tile by row index
-            int k = off;
+        if (khi >= LE) {
+            // Rank klo is the LAST of its bucket and rank khi the first value above it: v_lo = the bucket's maximum,
+            // v_hi = the minimum of the next two buckets (w2) — no ranking, no candidate list; an empty w2 (rare)
+            // leaves the scan over all valid values above v_lo.
+            const unsigned up = prefix + 3u > 127u ? 127u : prefix + 3u;
+            const unsigned cC = (128u - up) * 0x01010101u;
+            unsigned w2[2] = {0u, 0u};
+#pragma unroll
+            for (int q = 0; q < W3_NKW; ++q) {
+                const unsigned fl = (kw[q] + cB) & ~(kw[q] + cC) & 0x80808080u;
+                w2[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
+            }
+            in_t vmx = std::numeric_limits<in_t>::lowest(), vmn = w3_never_less<in_t>();
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                unsigned bits = wm[h];
+                unsigned bits = w1[h];
                 while (bits) {
                     const int pos = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    lcw[k++] = w3_value(src0, src1, 32 * h + pos);
+                    vmx = vmax(vmx, w3_value(src0, src1, 32 * h + pos));
+                }
+                bits = w2[h];
+                while (bits) {
+                    const int pos = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    vmn = vmin(vmn, w3_value(src0, src1, 32 * h + pos));
                 }
             }
-            if (w.part == 0) {                    // four sentinels behind the last candidate: the ranking reads 4 slots a trip
-                const in_t big = w3_never_less<in_t>();
-                lcw[m] = big; lcw[m + 1] = big; lcw[m + 2] = big; lcw[m + 3] = big;
-            }
-            __syncwarp(w.cmask);
-            // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
-            int b1 = -1, b2 = -1;
-            for (int base = w.part; base < m; base += W2_RANKW * 4) {
-                in_t v[W2_RANKW];
-                int rr[W2_RANKW];
-#pragma unroll
-                for (int t = 0; t < W2_RANKW; ++t) {
-                    const int a = base + t * 4;
-                    v[t] = lcw[a < m ? a : base];
-                    rr[t] = 0;
-                }
-#pragma unroll 1
-                for (int b = 0; b < m; b += 4) {
-                    const int4 raw = *reinterpret_cast<const int4 *>(lcw + b);
-                    in_t u[4];
-                    memcpy(u, &raw, 16);
-#pragma unroll
-                    for (int s = 0; s < 4; ++s) {
-#pragma unroll
-                        for (int t = 0; t < W2_RANKW; ++t) count_lt(rr[t], u[s], v[t]);
-                    }
-                }
-#pragma unroll
-                for (int t = 0; t < W2_RANKW; ++t) {
-                    const int a = base + t * 4;
-                    if (a < m) {                      // largest (rank, slot) code with rank <= j1 / j2
-                        const int code = (rr[t] << 8) | a;
-                        if (rr[t] <= j1 && code > b1) b1 = code;
-                        if (rr[t] <= j2 && code > b2) b2 = code;
-                    }
-                }
-            }
-            auto imax = [](int a, int b) { return a > b ? a : b; };
-            b1 = w3_col_reduce(w, b1, imax);
-            b2 = w3_col_reduce(w, b2, imax);
-            v_lo = lcw[b1 & 0xff];
-            v_hi = lcw[b2 & 0xff];
-            rescue = j2 >= m;             // rank khi above the window: every rank is <= j2 then, so v_hi is the
-            thr = v_hi;                   // window's largest value, the threshold of the rescue scan
-            __syncwarp(w.cmask);          // the list may be overwritten by the next selection
+            v_lo = w3_col_reduce(w, vmx, [](in_t a, in_t b) { return vmax(a, b); });
+            v_hi = w3_col_reduce(w, vmn, [](in_t a, in_t b) { return vmin(a, b); });
+            rescue = v_hi == w3_never_less<in_t>();
+            thr = v_lo;
         } else {
-            // crowded window (rare): its value range decides between "all one value" and a finer re-keying
-            uint32_t kmin = 0xffffffffu, kmax = 0u;
+            // both order statistics lie in the bucket, which holds m = LE - L values
+            const int m = LE - L;
+            const int j1 = klo - L, j2 = khi - L;
+            if (m <= W3_CAP) {
+                // slot offset of this part = candidates of the lower parts
+                const int mine = __popc(w1[0]) + __popc(w1[1]);
+                int off = 0;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                unsigned bits = wm[h];
-                while (bits) {
-                    const int pos = __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    const uint32_t kx = okey(w3_value(src0, src1, 32 * h + pos));
-                    kmin = kx < kmin ? kx : kmin;
-                    kmax = kx > kmax ? kx : kmax;
+                for (int q = 0; q < 3; ++q) {
+                    const int cq = __shfl_sync(w.cmask, mine, w.lane_base + 8 * q);
+                    if (q < w.part) off += cq;
                 }
-            }
-            kmin = w3_col_reduce(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
-            kmax = w3_col_reduce(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
-            in_t a, b;
-            unkey(kmin, a);
-            unkey(kmax, b);
-            typename Key::Scale sc;
-            if (!(b > a)) {                       // the whole window is one value
-                v_lo = a;
-                v_hi = a;
-                thr = a;
-                rescue = j2 >= m;
-            } else if (!Key::make(a, b, sc)) {
-                return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
+                // values of this part's bucket rows -> slots off.., fetched from the tile by row index
+                int k = off;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    unsigned bits = w1[h];
+                    while (bits) {
+                        const int pos = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        lcw[k++] = w3_value(src0, src1, 32 * h + pos);
+                    }
+                }
+                if (w.part == 0) {                // four sentinels behind the last candidate: the ranking reads 4 slots a trip
+                    const in_t big = w3_never_less<in_t>();
+                    lcw[m] = big; lcw[m + 1] = big; lcw[m + 2] = big; lcw[m + 3] = big;
+                }
+                __syncwarp(w.cmask);
+                // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
+                int b1 = -1, b2 = -1;
+                for (int a = w.part; a < m; a += 4) {
+                    const in_t v = lcw[a];
+                    int rr = 0;
+#pragma unroll 1
+                    for (int b = 0; b < m; b += 4) {
+                        const int4 raw = *reinterpret_cast<const int4 *>(lcw + b);
+                        in_t u[4];
+                        memcpy(u, &raw, 16);
+#pragma unroll
+                        for (int s4 = 0; s4 < 4; ++s4) count_lt(rr, u[s4], v);
+                    }
+                    const int code = (rr << 8) | a;       // largest (rank, slot) code with rank <= j1 / j2
+                    if (rr <= j1 && code > b1) b1 = code;
+                    if (rr <= j2 && code > b2) b2 = code;
+                }
+                auto imax = [](int a, int b) { return a > b ? a : b; };
+                b1 = w3_col_reduce(w, b1, imax);
+                b2 = w3_col_reduce(w, b2, imax);
+                v_lo = lcw[b1 & 0xff];
+                v_hi = lcw[b2 & 0xff];
+                __syncwarp(w.cmask);              // the list may be overwritten by the next selection
             } else {
-                w3_build_keys<Tr, false, FULL, true, false>(nullptr, src0, src1, kw, w.N, w.part, a, b, sc);
-                refined = true;
-                continue;
+                // crowded bucket (ties, clusters): its value range decides between "all one value" and a finer re-keying
+                uint32_t kmin = 0xffffffffu, kmax = 0u;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    unsigned bits = w1[h];
+                    while (bits) {
+                        const int pos = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        const uint32_t kx = okey(w3_value(src0, src1, 32 * h + pos));
+                        kmin = kx < kmin ? kx : kmin;
+                        kmax = kx > kmax ? kx : kmax;
+                    }
+                }
+                kmin = w3_col_reduce(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+                kmax = w3_col_reduce(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
+                in_t a, b;
+                unkey(kmin, a);
+                unkey(kmax, b);
+                typename Key::Scale sc;
+                if (!(b > a)) {                   // the whole bucket is one value
+                    v_lo = a;
+                    v_hi = a;
+                } else if (!Key::make(a, b, sc)) {
+                    return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
+                } else {
+                    w3_build_keys<Tr, false, FULL, true, false>(nullptr, src0, src1, kw, w.N, w.part, a, b, sc);
+                    refined = true;
+                    continue;
+                }
             }
         }
         if (rescue) {                             // rank khi lies above the window: smallest valid value above it
@@ -369,13 +384,18 @@ __host__ __device__ inline W3Smem w3_smem_layout(size_t vs) {
     s.patch = take(W3_ROWS, 16);                          // [part][value]: 0x7f where the row is dropped
     s.misc = take(16, 16);                                // stw[2], sel
     s.keep = take(W3_ROWS, 16);
-    s.bar = take(32, 16);                                 // full, empty, xbar[2]
+    s.bar = take(48, 16);                                 // full, xbar[2], (spare), arrival counter
     s.total = off;
     return s;
 }
 
-template <class Tr, bool FULL>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(W3_THREADS, 2)
+// NCTA: resident CTAs per SM the compiler makes room for (3 -> 80 registers: fp32, whose shared memory fits three times;
+// 2 -> 128 registers: the fixed form with its 64-bit risks)
+// three CTAs fit an SM when the layout stays under 75 KB (228 KB per SM, 1 KB reserved per CTA)
+__host__ __device__ constexpr int w3_ctas_per_sm(size_t vs) { return vs == 4 ? 3 : 2; }
+
+template <class Tr, bool FULL, int NCTA>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(W3_THREADS, NCTA)
 consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
@@ -405,8 +425,8 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     int *sel_s = stw_s + 2;
     uint8_t *keep_s = smem_raw + S.keep;
     u64 *full_bar = reinterpret_cast<u64 *>(smem_raw + S.bar);
-    u64 *empty_bar = full_bar + 1;
-    u64 *xbar = full_bar + 2;                                        // [2] by round parity
+    u64 *xbar = full_bar + 1;                                        // [2] by round parity
+    unsigned *done_s = reinterpret_cast<unsigned *>(full_bar + 4);   // warps that have made their last read of the tile
 
     // this thread's column unit: column c of the CTA's 64, rows 8k + 2*part + {0, 1}
     const int cc = lane & 7;
@@ -435,7 +455,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     if (tid == 0) {
         if (smem_u32(tile_s) & 1023u) __trap();      // the swizzle pattern is a function of the address bits
         mbar_init(full_bar, 1);
-        mbar_init(empty_bar, W3_THREADS);
+        *done_s = 0u;
         mbar_init(xbar, 1);
         mbar_init(xbar + 1, 1);
         stw_s[0] = STW_OK;
@@ -448,6 +468,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     // the peer must be running (its barriers initialised) before anything is sent into its shared memory
     cluster_sync_all();
 
+    constexpr int NS = W3_ROWS / 32;
     const bool shape2 = second_pass_shape_panic(p);
     const bool high = p.tie == SVOC_TIE_HIGH_INDEX_KEPT;
     const uint32_t theirs_remote = map_to_peer(smem_u32(theirs_s), peer);
@@ -596,7 +617,6 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
             // ---- phase 3: which rows are kept — warp 0 (w2_select_rows) while warp 1 does the first-pass reliability;
             //      exact all-pairs ranking when the selection gives up on this round's risks.  Both CTAs of the pair
             //      compute the same thing from the same risks; rank 0 writes the per-round outputs.
-            constexpr int NS = W3_ROWS / 32;
             if (warp == 0) {
                 unsigned words[NS];
                 acc_t qrow[NS];
@@ -654,40 +674,6 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                 keep_s[tid] = kept ? 1 : 0;
                 patch_s[((tid >> 1) & 3) * W3_NV + 2 * (tid >> 3) + (tid & 1)] = kept ? 0 : 0x7f;
             }
-            // second-pass reliability, mask and status
-            if (warp == 0) {
-                acc_t s2 = 0;
-#pragma unroll
-                for (int j = 0; j < NS; ++j)
-                    if (j * 32 + lane < N && ((maskw[j] >> lane) & 1u)) s2 += qr_s[j * 32 + lane];
-                if (rank == 0 && p.reliable && lane < p.words) p.reliable[(size_t)r * p.words + lane] = maskw[lane];
-                for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-                if (lane == 0) {
-                    int stw = STW_OK;
-                    if constexpr (Tr::fixed) {
-                        i64 rel2 = 0;
-                        if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-                        else {
-                            rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
-                            if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
-                        }
-                        if (rank == 0) reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
-                    } else {
-                        val_t rel2 = 0;
-                        if (shape2) stw = min(stw, STW_SECOND_SHAPE);
-                        else {
-                            rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
-                            if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
-                        }
-                        if (rank == 0) reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
-                    }
-                    if (stw != STW_OK) atomicMin(stw_s + par, stw);
-                    if (rank == 0) {         // nothing later contributes to the status
-                        const int sw = stw_s[par];
-                        p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
-                    }
-                }
-            }
             __syncthreads();                 // keep_s / patch_s are complete
             // ---- phase 4 set-up: keys of the kept rows only; the loop then runs the second-pass centre
             if (shape2) {
@@ -709,21 +695,55 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                 }
             }
         }
-        // ---- this thread has made its last read of the tile; once all have, the next round is copied in.  The WHOLE
-        //      warp 0 waits: were lane 0 alone to spin here while its 31 siblings spin on the full barrier at the top
-        //      of the next round — which only lane 0's copy can complete — the warp would depend on the hardware
-        //      switching between its two divergent spin loops (it hung, rarely: whenever another warp was last).
-        mbar_arrive(empty_bar);
-        if (warp == 0 && has_next) {
-            mbar_wait(empty_bar, par);
-            if (lane == 0) {
+        // ---- this warp has made its last read of the tile: the LAST warp to get here copies the next round in
+        //      (an arrival counter; nobody waits — an earlier version had warp 0 wait on an "empty" mbarrier, and with
+        //      lane 0 alone waiting while its siblings span on the full barrier that only lane 0's copy completes,
+        //      the kernel hung whenever another warp was last: divergent spin loops inside one warp)
+        __syncwarp();
+        if (lane == 0 && has_next) {
+            if (atomicAdd(done_s, 1u) == W3_THREADS / 32 - 1) {
+                *done_s = 0u;
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_expect_tx(full_bar, tile_bytes);
                 const int row0 = (int)((r + n_clusters) * p.N);
                 tma_load_box(tile_s, &tmap, (int)rank * W3_COLS, row0, full_bar);
                 tma_load_box(tile_s + W3_BOX_WORDS, &tmap, (int)rank * W3_COLS + 32, row0, full_bar);
             }
-            __syncwarp();
+        }
+        __syncwarp();
+        // ---- second-pass reliability, mask and status: warp 0, at the end of the round so that it delays no barrier
+        if (warp == 0) {
+            acc_t s2 = 0;
+#pragma unroll
+            for (int j = 0; j < NS; ++j)
+                if (j * 32 + lane < N && ((maskw[j] >> lane) & 1u)) s2 += qr_s[j * 32 + lane];
+            if (rank == 0 && p.reliable && lane < p.words) p.reliable[(size_t)r * p.words + lane] = maskw[lane];
+            for (int o = 16; o; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            if (lane == 0) {
+                int stw = STW_OK;
+                if constexpr (Tr::fixed) {
+                    i64 rel2 = 0;
+                    if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                    else {
+                        rel2 = reliability_fixed(s2 / (u64)R, p, STW_SQRT_REL2, stw);
+                        if (rel2 < 0 || rel2 > WSAD) stw = min(stw, STW_REL2_RANGE);
+                    }
+                    if (rank == 0) reinterpret_cast<i64 *>(p.rel2)[r] = rel2;
+                } else {
+                    val_t rel2 = 0;
+                    if (shape2) stw = min(stw, STW_SECOND_SHAPE);
+                    else {
+                        rel2 = reliability_float<val_t>(s2 / (val_t)R, p);
+                        if (!(rel2 >= 0 && rel2 <= 1)) stw = min(stw, STW_REL2_RANGE);
+                    }
+                    if (rank == 0) reinterpret_cast<val_t *>(p.rel2)[r] = rel2;
+                }
+                if (stw != STW_OK) atomicMin(stw_s + par, stw);
+                if (rank == 0) {         // nothing later contributes to the status
+                    const int sw = stw_s[par];
+                    p.status[r] = (sw == STW_OK) ? SVOC_ST_OK : (sw & 0xff);
+                }
+            }
         }
     }
 }
@@ -747,7 +767,8 @@ int launch_wide3(const Params &p, const Plan &pl, cudaStream_t st) {
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with code " + std::to_string((int)cr));
-    void (*kern)(const Params, const CUtensorMap) = (p.N == W3_ROWS) ? consensus_wide3_kernel<Tr, true> : consensus_wide3_kernel<Tr, false>;
+    constexpr int NCTA = w3_ctas_per_sm(sizeof(typename Tr::acc_t));
+    void (*kern)(const Params, const CUtensorMap) = (p.N == W3_ROWS) ? consensus_wide3_kernel<Tr, true, NCTA> : consensus_wide3_kernel<Tr, false, NCTA>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, W3_THREADS, pl.smem, st>>>(p, tmap);

@@ -139,7 +139,8 @@ static bool plan_wide3(const svoc_config &c, const void *pred, const svoc_output
     pl.npad = 0;
     pl.tile_smem = 1;
     pl.wP = 4; pl.wRP = 64; pl.wCS = 0; pl.wH = 1;
-    pl.grid = 2 * std::min<long long>(T, (long long)sm_count());      // clusters of two CTAs, two CTAs per SM
+    // clusters of two CTAs; as many clusters as the SMs hold at once (3 CTAs per SM for fp32, 2 for the fixed form)
+    pl.grid = 2 * std::min<long long>(T, (long long)sm_count() * w3_ctas_per_sm(c.dtype == SVOC_F32 ? 4 : 8) / 2);
     return true;
 }
 
