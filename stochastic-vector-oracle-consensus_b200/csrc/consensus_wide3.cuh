@@ -225,6 +225,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             const unsigned fl = (kw[q] + cA) & ~(kw[q] + cB) & 0x80808080u;
             w1[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
         }
+        // the two fetch loops below take TWO rows per trip (two independent loads in flight): a trip is a chain of
+        // find-first-set, address, load and compare, and the loops are latency-bound
         bool rescue = false;
         in_t thr = const_value;
         if (khi >= LE) {
@@ -246,13 +248,19 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 while (bits) {
                     const int pos = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    vmx = vmax(vmx, w3_value(src0, src1, 32 * h + pos));
+                    const int pos2 = bits ? __ffs(bits) - 1 : pos;       // an idle second slot re-reads the first row
+                    bits &= bits - 1;
+                    const in_t xa = w3_value(src0, src1, 32 * h + pos), xb = w3_value(src0, src1, 32 * h + pos2);
+                    vmx = vmax(vmx, vmax(xa, xb));
                 }
                 bits = w2[h];
                 while (bits) {
                     const int pos = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    vmn = vmin(vmn, w3_value(src0, src1, 32 * h + pos));
+                    const int pos2 = bits ? __ffs(bits) - 1 : pos;
+                    bits &= bits - 1;
+                    const in_t xa = w3_value(src0, src1, 32 * h + pos), xb = w3_value(src0, src1, 32 * h + pos2);
+                    vmn = vmin(vmn, vmin(xa, xb));
                 }
             }
             v_lo = w3_col_reduce(w, vmx, [](in_t a, in_t b) { return vmax(a, b); });
@@ -491,7 +499,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
         }
         // ---- phase 1a: the tile has landed; key scale from a 64-row sample (rows 0..63: the first 16 values of
         //      every part), then the keys
-        mbar_wait(full_bar, par);
+        mbar_wait_sleepy(full_bar, par);
         bool col_const = false, col_fb = false, refined1 = false;
         in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
         typename Key::Scale sc{};
@@ -605,7 +613,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                     }
                 }
             }
-            mbar_wait(xbar + par, (it >> 1) & 1u);
+            mbar_wait_sleepy(xbar + par, (it >> 1) & 1u);
             {
                 const acc_t other = theirs_s[par * W3_ROWS + my_row];
                 const acc_t q = rank == 0 ? own + other : other + own;        // partial(rank 0) + partial(rank 1) on both CTAs

@@ -183,6 +183,21 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// The same wait for a barrier that usually completes MUCH later (a tile copy, a peer CTA's data): try_wait takes a
+// suspend-time hint, so the warp sleeps in hardware instead of spinning through issue slots its neighbours could use
+__device__ __forceinline__ void mbar_wait_sleepy(u64 *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "SWAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+        "@p bra SDONE_%=;\n"
+        "bra SWAIT_%=;\n"
+        "SDONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity), "r"(20000u)
+        : "memory");
+}
 __device__ __forceinline__ void mbar_wait(u64 *bar, uint32_t parity) {
     asm volatile(
         "{\n"
