@@ -38,37 +38,63 @@
 
 namespace svoc {
 
-constexpr int W3_THREADS = 256;
 constexpr int W3_COLS = 64;          // columns per CTA
+#ifndef W3_DEFAULT_LANES
+#define W3_DEFAULT_LANES 4
+#endif
 constexpr int W3_D = 128;            // columns per round (two CTAs)
 constexpr int W3_ROWS = 256;         // rows of a landing box (rows >= N are ignored)
-constexpr int W3_NV = 64;            // values per thread
-constexpr int W3_NKW = 16;           // packed key words per thread
 constexpr int W3_CAP = 16;           // candidate slots per column (one key bucket; fuller buckets are re-keyed)
 constexpr int W3_LSTRIDE = 20;       // words per column in the candidate list: 16 slots + 4 sentinels; 20 * c mod 32 takes
                                      // 8 different multiples of 4 for the 8 columns of a warp: conflict-free 128-bit reads
 constexpr int W3_BOX_BYTES = 32 * W3_ROWS * 4;     // one 32-column box
 constexpr int W3_BOX_WORDS = W3_BOX_BYTES / 4;
 
+// Geometry for P lanes per column (P = 4: 256 threads, 64 values per thread, up to 128 registers; P = 8: 512 threads,
+// 32 values per thread, 64 registers).  A thread owns, of every group of 8 rows, the E = 8 / P consecutive rows
+// E*part .. E*part + E - 1: with the 128-byte swizzle (16-byte chunk index XOR row mod 8) the 32 lanes of a warp —
+// 32 / P adjacent columns x P parts — then read 32 different banks.
+template <int P>
+struct W3Geo {
+    static constexpr int LANES = P;
+    static constexpr int THREADS = W3_COLS * P;
+    static constexpr int WARPS = THREADS / 32;
+    static constexpr int CW = 32 / P;              // columns per warp
+    static constexpr int NV = W3_ROWS / P;         // values per thread
+    static constexpr int NKW = NV / 4;             // packed key words per thread
+    static constexpr int E = 8 / P;                // consecutive rows per thread in a group of 8
+    static constexpr int MW = (NKW + 7) / 8;       // 32-bit words of a thread's row mask
+    static constexpr int RT = THREADS / 16;        // rows per trip of the risk sweep (16 lanes share a row)
+    static constexpr int NT = W3_ROWS / RT;        // trips
+};
+
 struct W3Ctx {
     int N;
-    int part;            // 0..3: rows 8k + 2*part + {0, 1}
-    unsigned cmask;      // the four lanes of this thread's column
+    int part;            // which rows of every 8-row group
+    unsigned cmask;      // the lanes of this thread's column
     int lane_base;       // lane of part 0 of this column
 };
 
-__device__ __forceinline__ int w3_row(int j, int part) { return 8 * (j >> 1) + 2 * part + (j & 1); }
+template <int P>
+__device__ __forceinline__ int w3_row(int j, int part) {
+    constexpr int E = W3Geo<P>::E;
+    return 8 * (j / E) + E * part + (j % E);
+}
 
-template <class T>
+template <int P, class T>
 __device__ __forceinline__ T w3_col_sum(const W3Ctx &w, T v) {
-    v += __shfl_xor_sync(w.cmask, v, 8);
-    v += __shfl_xor_sync(w.cmask, v, 16);
+    constexpr int CW = W3Geo<P>::CW;
+    v += __shfl_xor_sync(w.cmask, v, CW);
+    v += __shfl_xor_sync(w.cmask, v, 2 * CW);
+    if (P == 8) v += __shfl_xor_sync(w.cmask, v, 4 * CW);
     return v;
 }
-template <class T, class Op>
+template <int P, class T, class Op>
 __device__ __forceinline__ T w3_col_reduce(const W3Ctx &w, T v, Op op) {
-    v = op(v, __shfl_xor_sync(w.cmask, v, 8));
-    v = op(v, __shfl_xor_sync(w.cmask, v, 16));
+    constexpr int CW = W3Geo<P>::CW;
+    v = op(v, __shfl_xor_sync(w.cmask, v, CW));
+    v = op(v, __shfl_xor_sync(w.cmask, v, 2 * CW));
+    if (P == 8) v = op(v, __shfl_xor_sync(w.cmask, v, 4 * CW));
     return v;
 }
 
@@ -122,58 +148,63 @@ __device__ __noinline__ typename Tr::val_t w3_exact_centre(const typename Tr::in
     return column_centre_generic<Tr>(gcol, W3_D, N, keep, n_valid, kind, false, sk, ku, stw);
 }
 
-// this thread's value j (row 8*(j>>1) + 2*part + (j&1)) in the swizzled tile
-template <class in_t>
+// this thread's value j in the swizzled tile: src0 points at its first row, src1 at its second row of the same group
+// of 8 (E = 2 only; the two differ by one 128-byte line and the change of the swizzled chunk)
+template <int P, class in_t>
 __device__ __forceinline__ in_t w3_value(const in_t *src0, const in_t *src1, int j) {
+    constexpr int E = W3Geo<P>::E;
+    if (E == 1) return src0[j * 256];
     return ((j & 1) ? src1 : src0)[(j >> 1) * 256];
 }
 
 // ---- keys in registers
 // FROM_REGS: the values are passed in x (first build of a round); otherwise they are read from the tile.
 // ONLY_VALID: rows whose current key is the sentinel (dropped / padded) keep it.
-template <class Tr, bool FIRST, bool FULL, bool ONLY_VALID, bool FROM_REGS>
-__device__ __forceinline__ void w3_build_keys(const typename Tr::in_t *x, const typename Tr::in_t *src0,
-                                              const typename Tr::in_t *src1, unsigned (&kw)[W3_NKW], int N, int part,
+template <class Tr, int P, bool FIRST, bool FULL, bool ONLY_VALID, bool FROM_REGS>
+__device__ __forceinline__ void w3_build_keys(const typename Tr::in_t *x, const typename Tr::in_t *src0, const typename Tr::in_t *src1,
+                                              unsigned (&kw)[W3Geo<P>::NKW], int N, int part,
                                               typename Tr::in_t lo, typename Tr::in_t hi,
                                               const typename WideKey<Tr>::Scale &sc) {
 #pragma unroll
-    for (int q = 0; q < W3_NKW; ++q) {
+    for (int q = 0; q < W3Geo<P>::NKW; ++q) {
         unsigned f[4];
         const unsigned old = kw[q];
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             const int j = 4 * q + b;
-            const typename Tr::in_t xv = FROM_REGS ? x[j] : w3_value(src0, src1, j);
+            const typename Tr::in_t xv = FROM_REGS ? x[j] : w3_value<P>(src0, src1, j);
             f[b] = wide_key<Tr, FIRST>(xv, lo, hi, sc);        // pack4 takes the low byte
-            if (!FULL && w3_row(j, part) >= N) f[b] = 127u;
+            if (!FULL && w3_row<P>(j, part) >= N) f[b] = 127u;
             if (ONLY_VALID && ((old >> (8 * b)) & 0xffu) == 127u) f[b] = 127u;
         }
         kw[q] = pack4(f[0], f[1], f[2], f[3]);
     }
 }
 
-__device__ __forceinline__ int w3_key_sum(const unsigned (&kw)[W3_NKW]) {
+template <int NKW>
+__device__ __forceinline__ int w3_key_sum(const unsigned (&kw)[NKW]) {
     unsigned a0 = 0, a1 = 0;
 #pragma unroll
-    for (int q = 0; q < W3_NKW; q += 2) {
+    for (int q = 0; q < NKW; q += 2) {
         a0 = __dp4a(kw[q], 0x01010101u, a0);
         a1 = __dp4a(kw[q + 1], 0x01010101u, a1);
     }
     return (int)(a0 + a1);
 }
 
-// #(key >= cand) among this thread's 64 keys — see count_ge in consensus_wide.cuh for the SWAR identity
-__device__ __forceinline__ int w3_count_ge(const unsigned (&kw)[W3_NKW], unsigned cand, int sum_keys) {
+// #(key >= cand) among this thread's keys — see count_ge in consensus_wide.cuh for the SWAR identity
+template <int NKW>
+__device__ __forceinline__ int w3_count_ge(const unsigned (&kw)[NKW], unsigned cand, int sum_keys) {
     const unsigned cb = (128u - cand) * 0x01010101u;
     int a0 = 0, a1 = 0, a2 = 0, a3 = 0;
 #pragma unroll
-    for (int q = 0; q < W3_NKW; q += 4) {
+    for (int q = 0; q < NKW; q += 4) {
         a0 = __dp4a((int)__viaddmax_u32(kw[q], cb, 0u), 0x01010101, a0);
         a1 = __dp4a((int)__viaddmax_u32(kw[q + 1], cb, 0u), 0x01010101, a1);
         a2 = __dp4a((int)__viaddmax_u32(kw[q + 2], cb, 0u), 0x01010101, a2);
         a3 = __dp4a((int)__viaddmax_u32(kw[q + 3], cb, 0u), 0x01010101, a3);
     }
-    return (int)((unsigned)(sum_keys + W3_NV * (int)(128u - cand) - ((a0 + a1) + (a2 + a3))) >> 8);
+    return (int)((unsigned)(sum_keys + 4 * NKW * (int)(128u - cand) - ((a0 + a1) + (a2 + a3))) >> 8);
 }
 
 template <class T> __device__ __forceinline__ T w3_never_less();
@@ -182,11 +213,11 @@ template <> __device__ __forceinline__ int32_t w3_never_less<int32_t>() { return
 
 // Centre of the valid rows of this thread's column (valid = key != sentinel: all rows < N in the first pass, the
 // kept rows in the second).  Executed by the four lanes of the column together; every one returns the result.
-// src0 / src1: this thread's even / odd rows in the tile.  gcol / keep serve only the rare exact fallback, which
+// src0 / src1: this thread's rows in the tile (w3_value).  gcol / keep serve only the rare exact fallback, which
 // walks the column in global memory.  lcw: this column's candidate list (W3_LSTRIDE words).
-template <class Tr, bool FULL>
-__device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const typename Tr::in_t *src0,
-                                                        const typename Tr::in_t *src1, unsigned (&kw)[W3_NKW],
+template <class Tr, int P, bool FULL>
+__device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const typename Tr::in_t *src0, const typename Tr::in_t *src1,
+                                                        unsigned (&kw)[W3Geo<P>::NKW],
                                                         const typename Tr::in_t *gcol, const uint8_t *keep, int n_valid,
                                                         int kind, bool col_const, bool col_fallback,
                                                         typename Tr::in_t const_value, typename Tr::in_t *lcw,
@@ -194,6 +225,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using Key = WideKey<Tr>;
+    using G = W3Geo<P>;
+    constexpr int NKW = G::NKW, MW = G::MW;
     refined = false;
     if (col_const) return Tr::half_sum((val_t)const_value, (val_t)const_value);
     if (col_fallback) return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
@@ -209,8 +242,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
 #pragma unroll
         for (int bit = 6; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
-            const int ge = w3_col_sum(w, w3_count_ge(kw, cand, sum_keys));
-            const int lt = 4 * W3_NV - ge;        // sentinels (127) are never below a pivot
+            const int ge = w3_col_sum<P>(w, w3_count_ge(kw, cand, sum_keys));
+            const int lt = W3_ROWS - ge;        // sentinels (127) are never below a pivot
             if (lt <= klo) { prefix = cand; L = lt; }
             else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
         }
@@ -219,9 +252,9 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
         //      w1 = rows whose key is `prefix`.
         const unsigned cA = (128u - prefix) * 0x01010101u;            // byte MSB set <=> key >= prefix
         const unsigned cB = cA - 0x01010101u;                         //              <=> key >= prefix + 1
-        unsigned w1[2] = {0u, 0u};
+        unsigned w1[MW] = {};
 #pragma unroll
-        for (int q = 0; q < W3_NKW; ++q) {
+        for (int q = 0; q < NKW; ++q) {
             const unsigned fl = (kw[q] + cA) & ~(kw[q] + cB) & 0x80808080u;
             w1[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
         }
@@ -235,22 +268,22 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             // leaves the scan over all valid values above v_lo.
             const unsigned up = prefix + 3u > 127u ? 127u : prefix + 3u;
             const unsigned cC = (128u - up) * 0x01010101u;
-            unsigned w2[2] = {0u, 0u};
+            unsigned w2[MW] = {};
 #pragma unroll
-            for (int q = 0; q < W3_NKW; ++q) {
+            for (int q = 0; q < NKW; ++q) {
                 const unsigned fl = (kw[q] + cB) & ~(kw[q] + cC) & 0x80808080u;
                 w2[q >> 3] += ((fl * 0x00204081u) >> 28) << (4 * (q & 7));
             }
             in_t vmx = std::numeric_limits<in_t>::lowest(), vmn = w3_never_less<in_t>();
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < MW; ++h) {
                 unsigned bits = w1[h];
                 while (bits) {
                     const int pos = __ffs(bits) - 1;
                     bits &= bits - 1;
                     const int pos2 = bits ? __ffs(bits) - 1 : pos;       // an idle second slot re-reads the first row
                     bits &= bits - 1;
-                    const in_t xa = w3_value(src0, src1, 32 * h + pos), xb = w3_value(src0, src1, 32 * h + pos2);
+                    const in_t xa = w3_value<P>(src0, src1, 32 * h + pos), xb = w3_value<P>(src0, src1, 32 * h + pos2);
                     vmx = vmax(vmx, vmax(xa, xb));
                 }
                 bits = w2[h];
@@ -259,12 +292,12 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     bits &= bits - 1;
                     const int pos2 = bits ? __ffs(bits) - 1 : pos;
                     bits &= bits - 1;
-                    const in_t xa = w3_value(src0, src1, 32 * h + pos), xb = w3_value(src0, src1, 32 * h + pos2);
+                    const in_t xa = w3_value<P>(src0, src1, 32 * h + pos), xb = w3_value<P>(src0, src1, 32 * h + pos2);
                     vmn = vmin(vmn, vmin(xa, xb));
                 }
             }
-            v_lo = w3_col_reduce(w, vmx, [](in_t a, in_t b) { return vmax(a, b); });
-            v_hi = w3_col_reduce(w, vmn, [](in_t a, in_t b) { return vmin(a, b); });
+            v_lo = w3_col_reduce<P>(w, vmx, [](in_t a, in_t b) { return vmax(a, b); });
+            v_hi = w3_col_reduce<P>(w, vmn, [](in_t a, in_t b) { return vmin(a, b); });
             rescue = v_hi == w3_never_less<in_t>();
             thr = v_lo;
         } else {
@@ -273,22 +306,24 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
             const int j1 = klo - L, j2 = khi - L;
             if (m <= W3_CAP) {
                 // slot offset of this part = candidates of the lower parts
-                const int mine = __popc(w1[0]) + __popc(w1[1]);
+                int mine = 0;
+#pragma unroll
+                for (int h = 0; h < MW; ++h) mine += __popc(w1[h]);
                 int off = 0;
 #pragma unroll
-                for (int q = 0; q < 3; ++q) {
-                    const int cq = __shfl_sync(w.cmask, mine, w.lane_base + 8 * q);
+                for (int q = 0; q < P - 1; ++q) {
+                    const int cq = __shfl_sync(w.cmask, mine, w.lane_base + G::CW * q);
                     if (q < w.part) off += cq;
                 }
                 // values of this part's bucket rows -> slots off.., fetched from the tile by row index
                 int k = off;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
+                for (int h = 0; h < MW; ++h) {
                     unsigned bits = w1[h];
                     while (bits) {
                         const int pos = __ffs(bits) - 1;
                         bits &= bits - 1;
-                        lcw[k++] = w3_value(src0, src1, 32 * h + pos);
+                        lcw[k++] = w3_value<P>(src0, src1, 32 * h + pos);
                     }
                 }
                 if (w.part == 0) {                // four sentinels behind the last candidate: the ranking reads 4 slots a trip
@@ -298,7 +333,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 __syncwarp(w.cmask);
                 // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
                 int b1 = -1, b2 = -1;
-                for (int a = w.part; a < m; a += 4) {
+                for (int a = w.part; a < m; a += P) {
                     const in_t v = lcw[a];
                     int rr = 0;
 #pragma unroll 1
@@ -314,8 +349,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     if (rr <= j2 && code > b2) b2 = code;
                 }
                 auto imax = [](int a, int b) { return a > b ? a : b; };
-                b1 = w3_col_reduce(w, b1, imax);
-                b2 = w3_col_reduce(w, b2, imax);
+                b1 = w3_col_reduce<P>(w, b1, imax);
+                b2 = w3_col_reduce<P>(w, b2, imax);
                 v_lo = lcw[b1 & 0xff];
                 v_hi = lcw[b2 & 0xff];
                 __syncwarp(w.cmask);              // the list may be overwritten by the next selection
@@ -323,18 +358,18 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 // crowded bucket (ties, clusters): its value range decides between "all one value" and a finer re-keying
                 uint32_t kmin = 0xffffffffu, kmax = 0u;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
+                for (int h = 0; h < MW; ++h) {
                     unsigned bits = w1[h];
                     while (bits) {
                         const int pos = __ffs(bits) - 1;
                         bits &= bits - 1;
-                        const uint32_t kx = okey(w3_value(src0, src1, 32 * h + pos));
+                        const uint32_t kx = okey(w3_value<P>(src0, src1, 32 * h + pos));
                         kmin = kx < kmin ? kx : kmin;
                         kmax = kx > kmax ? kx : kmax;
                     }
                 }
-                kmin = w3_col_reduce(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
-                kmax = w3_col_reduce(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
+                kmin = w3_col_reduce<P>(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+                kmax = w3_col_reduce<P>(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
                 in_t a, b;
                 unkey(kmin, a);
                 unkey(kmax, b);
@@ -345,7 +380,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 } else if (!Key::make(a, b, sc)) {
                     return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
                 } else {
-                    w3_build_keys<Tr, false, FULL, true, false>(nullptr, src0, src1, kw, w.N, w.part, a, b, sc);
+                    w3_build_keys<Tr, P, false, FULL, true, false>(nullptr, src0, src1, kw, w.N, w.part, a, b, sc);
                     refined = true;
                     continue;
                 }
@@ -354,15 +389,15 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
         if (rescue) {                             // rank khi lies above the window: smallest valid value above it
             uint32_t best = 0xffffffffu;
 #pragma unroll
-            for (int q = 0; q < W3_NKW; ++q) {
+            for (int q = 0; q < NKW; ++q) {
 #pragma unroll
                 for (int b = 0; b < 4; ++b) {
                     const bool valid = ((kw[q] >> (8 * b)) & 0xffu) != 127u;
-                    const in_t xv = w3_value(src0, src1, 4 * q + b);
+                    const in_t xv = w3_value<P>(src0, src1, 4 * q + b);
                     if (valid && xv > thr) { const uint32_t kx = okey(xv); best = kx < best ? kx : best; }
                 }
             }
-            best = w3_col_reduce(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+            best = w3_col_reduce<P>(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
             unkey(best, v_hi);
         }
         break;
@@ -382,8 +417,8 @@ __host__ __device__ inline W3Smem w3_smem_layout(size_t vs) {
     s.list = take((size_t)W3_COLS * W3_LSTRIDE * 4, 16);
     s.c1 = take((size_t)W3_COLS * vs, 16);                // first-pass centre of the CTA's columns
     s.theirs = take((size_t)2 * W3_ROWS * vs, 16);        // [parity][row]: the peer CTA's 64-column partial risks
-    s.xflag = take(2 * 8 * 4, 16);                        // [parity][warp]: the peer's input-range flags
-    s.lflag = take(2 * 8 * 4, 16);                        // [parity][warp]: this CTA's
+    s.xflag = take(2 * 16 * 4, 16);                       // [parity][warp]: the peer's input-range flags
+    s.lflag = take(2 * 16 * 4, 16);                       // [parity][warp]: this CTA's
     s.qr = take((size_t)W3_ROWS * vs, 16);
     s.wq = take((size_t)W2_RCAP * vs, 16);
     s.wi = take((size_t)W2_RCAP * 4, 16);
@@ -397,18 +432,20 @@ __host__ __device__ inline W3Smem w3_smem_layout(size_t vs) {
     return s;
 }
 
-// NCTA: resident CTAs per SM the compiler makes room for (3 -> 80 registers: fp32, whose shared memory fits three times;
-// 2 -> 128 registers: the fixed form with its 64-bit risks)
-// three CTAs fit an SM when the layout stays under 75 KB (228 KB per SM, 1 KB reserved per CTA)
-__host__ __device__ constexpr int w3_ctas_per_sm(size_t vs) { return vs == 4 ? 3 : 2; }
+// Resident CTAs per SM the compiler makes room for.  P = 4 lanes per column: three CTAs of 256 threads at 80 registers
+// for fp32, whose layout stays under 75 KB (228 KB per SM, 1 KB reserved per CTA), two at 128 registers for the
+// fixed form with its 64-bit risks.  P = 8: two CTAs of 512 threads at 64 registers.
+__host__ __device__ constexpr int w3_ctas_per_sm(int P, size_t vs) { return P == 8 ? 2 : (vs == 4 ? 3 : 2); }
 
-template <class Tr, bool FULL, int NCTA>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(W3_THREADS, NCTA)
+template <class Tr, int P, bool FULL>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(W3Geo<P>::THREADS, w3_ctas_per_sm(P, sizeof(typename Tr::acc_t)))
 consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
     using Key = WideKey<Tr>;
+    using G = W3Geo<P>;
+    constexpr int NV = G::NV, NKW = G::NKW, E = G::E, CW = G::CW, RT = G::RT, NT = G::NT;
     extern __shared__ __align__(1024) unsigned char smem_w3[];     // the 128-byte swizzle wants the boxes 1024-aligned
     unsigned char *const smem_raw = smem_w3;
     const W3Smem S = w3_smem_layout(sizeof(acc_t));
@@ -436,30 +473,31 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     u64 *xbar = full_bar + 1;                                        // [2] by round parity
     unsigned *done_s = reinterpret_cast<unsigned *>(full_bar + 4);   // warps that have made their last read of the tile
 
-    // this thread's column unit: column c of the CTA's 64, rows 8k + 2*part + {0, 1}
-    const int cc = lane & 7;
+    // this thread's column unit: column c of the CTA's 64, rows 8k + E*part + {0 .. E-1}
+    const int cq = lane % CW;
     W3Ctx w;
     w.N = N;
-    w.part = lane >> 3;
-    w.lane_base = cc;
-    w.cmask = 0x01010101u << cc;
+    w.part = lane / CW;
+    w.lane_base = cq;
+    w.cmask = (P == 8 ? 0x11111111u : 0x01010101u) << cq;
     const int part = w.part;
-    const int c = warp * 8 + cc;                  // column within the CTA
+    const int c = warp * CW + cq;                 // column within the CTA
     const int gc = (int)rank * W3_COLS + c;       // column within the round
     in_t *lcw = list + c * W3_LSTRIDE;
-    // tile addresses of this thread's two row phases (128-byte swizzle: the 16-byte chunk index of a row is XOR-ed
-    // with the row number mod 8, which is 2*part / 2*part + 1 for every row this thread reads)
+    // tile address of this thread's first row, and the step to its next row inside a group of 8 (128-byte swizzle: the
+    // 16-byte chunk index of a row is XOR-ed with the row number mod 8, which is E*part + e for every row read here)
     const int c32 = c & 31;
-    const in_t *src0 = tile_s + (c >> 5) * W3_BOX_WORDS + (2 * part) * 32 + ((((c32 >> 2) ^ (2 * part)) << 2) | (c32 & 3));
-    const in_t *src1 = tile_s + (c >> 5) * W3_BOX_WORDS + (2 * part + 1) * 32 + ((((c32 >> 2) ^ (2 * part + 1)) << 2) | (c32 & 3));
-    // this thread's row unit in the risk sweep: 4-column chunk rh of row 16*t + rg (t = 0..15); after the shuffle
-    // tree the thread holds the total of row 16*rh + rg
+    const in_t *src0 = tile_s + (c >> 5) * W3_BOX_WORDS + (E * part) * 32 + ((((c32 >> 2) ^ (E * part)) << 2) | (c32 & 3));
+    const in_t *src1 = E == 1 ? src0 : tile_s + (c >> 5) * W3_BOX_WORDS + (E * part + 1) * 32 + ((((c32 >> 2) ^ (E * part + 1)) << 2) | (c32 & 3));
+    // this thread's row unit in the risk sweep: 4-column chunk rh of row RT*t + rg (t = 0 .. NT-1); after the shuffle
+    // tree the thread holds the total of row RT * (rh >> (4 - log2 NT)) + rg
     const int rh = lane & 15, rg = warp * 2 + (lane >> 4);
     const in_t *rsrc = tile_s + (rh >> 3) * W3_BOX_WORDS + rg * 32 + (((rh & 7) ^ (rg & 7)) << 2);
-    const int my_row = 16 * rh + rg;
+    const int my_row = RT * (NT == 16 ? rh : rh >> 1) + rg;
+    const bool row_owner = NT == 16 || (rh & 1) == 0;     // NT = 8: two lanes end up with the same row total
 
     const uint32_t tile_bytes = 2 * W3_BOX_BYTES;
-    constexpr uint32_t XBYTES = W3_ROWS * sizeof(acc_t) + (Tr::fixed ? 8 * 4 : 0);
+    constexpr uint32_t XBYTES = W3_ROWS * sizeof(acc_t) + (Tr::fixed ? G::WARPS * 4 : 0);
     if (tid == 0) {
         if (smem_u32(tile_s) & 1023u) __trap();      // the swizzle pattern is a function of the address bits
         mbar_init(full_bar, 1);
@@ -503,44 +541,41 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
         bool col_const = false, col_fb = false, refined1 = false;
         in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
         typename Key::Scale sc{};
-        unsigned kw[W3_NKW];
+        unsigned kw[NKW];
         {
-            in_t x[W3_NV];
+            in_t x[NV];
 #pragma unroll
-            for (int k = 0; k < W3_NV / 2; ++k) {
-                x[2 * k] = src0[k * 256];             // 8 rows of 32 words
-                x[2 * k + 1] = src1[k * 256];
-            }
+            for (int j = 0; j < NV; ++j) x[j] = w3_value<P>(src0, src1, j);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
+            for (int j = 0; j < 64 / P; ++j) {       // rows 0..63
                 lo = vmin(lo, x[j]);
                 hi = vmax(hi, x[j]);
             }
-            lo = w3_col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
-            hi = w3_col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+            lo = w3_col_reduce<P>(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+            hi = w3_col_reduce<P>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
             if (!(hi > lo)) {                         // degenerate sample: exact sweep, which also detects a constant column
 #pragma unroll
-                for (int j = 0; j < W3_NV; ++j) {
-                    if (FULL || w3_row(j, part) < N) {
+                for (int j = 0; j < NV; ++j) {
+                    if (FULL || w3_row<P>(j, part) < N) {
                         lo = vmin(lo, x[j]);
                         hi = vmax(hi, x[j]);
                     }
                 }
-                lo = w3_col_reduce(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
-                hi = w3_col_reduce(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+                lo = w3_col_reduce<P>(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+                hi = w3_col_reduce<P>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
             }
             col_const = !(hi > lo);
             col_fb = !col_const && !Key::make(lo, hi, sc);
 #pragma unroll
-            for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
-            if (!col_const && !col_fb) w3_build_keys<Tr, true, FULL, false, true>(x, src0, src1, kw, N, part, lo, hi, sc);
+            for (int q = 0; q < NKW; ++q) kw[q] = 0u;
+            if (!col_const && !col_fb) w3_build_keys<Tr, P, true, FULL, false, true>(x, src0, src1, kw, N, part, lo, hi, sc);
         }
         // ---- the two passes share ONE inlined copy of the centre code: pass 0 = first-pass centre, risks, row
         //      selection, key patching; pass 1 = second-pass centre
 #pragma unroll 1
         for (int pass = 0;; ++pass) {
             bool refined = false;
-            const val_t ctr = w3_centre<Tr, FULL>(w, src0, src1, kw, gcol, pass ? keep_s : nullptr, pass ? R : N,
+            const val_t ctr = w3_centre<Tr, P, FULL>(w, src0, src1, kw, gcol, pass ? keep_s : nullptr, pass ? R : N,
                                                   pass ? p.centre2 : p.centre, col_const, col_fb, lo, lcw, refined);
             if (pass) {
                 if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = ctr;
@@ -554,20 +589,20 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
             __syncthreads();
 
             // ---- phase 2: quadratic risk.  Row-wise sweep of the tile: 16 lanes share a row (a quarter-warp reads
-            //      one 128-byte line), a thread visits rows 16t + rg, t = 0..15, and folds (x - e1)^2 over its four
-            //      columns; the 16 partials of a thread and the 16 lanes of a row are then folded together by a
+            //      one 128-byte line), a thread visits rows RT*t + rg, t = 0 .. NT-1, and folds (x - e1)^2 over its four
+            //      columns; the NT partials of a thread and the 16 lanes of a row are then folded together by a
             //      transposing shuffle tree (xor 8, 4, 2, 1: fixed order), which leaves every thread with the total
-            //      of ONE row over the CTA's 64 columns.
+            //      of ONE row over the CTA's 64 columns (NT = 8: pairs of lanes hold the same row; one of them owns it).
             acc_t own;
             {
                 val_t e4[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) e4[k] = c1_s[4 * rh + k];
-                acc_t v[16];
+                acc_t v[NT];
                 bool bad = false;
 #pragma unroll
-                for (int t = 0; t < 16; ++t) {
-                    const int4 raw = *reinterpret_cast<const int4 *>(rsrc + t * 16 * 32);
+                for (int t = 0; t < NT; ++t) {
+                    const int4 raw = *reinterpret_cast<const int4 *>(rsrc + t * RT * 32);
                     in_t xr[4];
                     memcpy(xr, &raw, 16);
                     acc_t q = 0;
@@ -576,40 +611,33 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                         if constexpr (Tr::fixed) {
                             const bool out = p.constrained ? ((xr[k] < 0) | ((i64)xr[k] > WSAD))
                                                            : (((i64)xr[k] > ENGINE_RANGE) | ((i64)xr[k] < -ENGINE_RANGE));
-                            bad |= out & (FULL || 16 * t + rg < N);
+                            bad |= out & (FULL || RT * t + rg < N);
                         }
                         q += Tr::dev(xr[k], e4[k]);
                     }
                     v[t] = q;
                 }
-                const bool b3 = rh & 8, b2 = rh & 4, b1 = rh & 2, b0 = rh & 1;
-                acc_t u8[8], u4[4], u2[2];
+                // halving steps: lane bit 3 keeps the upper / lower half of the trips, bit 2 of what is left, ...
+                int lanebit = 8;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {          // keep t = i + 8*b3
-                    const acc_t keep = b3 ? v[i + 8] : v[i], send = b3 ? v[i] : v[i + 8];
-                    u8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-                }
+                for (int n = NT / 2; n >= 1; n /= 2, lanebit >>= 1) {
+                    const bool up = rh & lanebit;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const acc_t keep = b2 ? u8[i + 4] : u8[i], send = b2 ? u8[i] : u8[i + 4];
-                    u4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                    for (int i = 0; i < n; ++i) {
+                        const acc_t keep = up ? v[i + n] : v[i], send = up ? v[i] : v[i + n];
+                        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, lanebit);
+                    }
                 }
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    const acc_t keep = b1 ? u4[i + 2] : u4[i], send = b1 ? u4[i] : u4[i + 2];
-                    u2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-                }
-                {
-                    const acc_t keep = b0 ? u2[1] : u2[0], send = b0 ? u2[0] : u2[1];
-                    own = keep + __shfl_xor_sync(0xffffffffu, send, 1);        // row 16*rh + rg
-                }
+                own = v[0];
+                if (NT == 8) own += __shfl_xor_sync(0xffffffffu, own, 1);     // both lanes of the pair: the same sum
                 // to the peer: this row's partial (and, fixed form, the warp's input-range flag)
-                st_async_peer(theirs_remote + (uint32_t)((par * W3_ROWS + my_row) * sizeof(acc_t)), own, xbar_remote + par * 8u);
+                if (row_owner)
+                    st_async_peer(theirs_remote + (uint32_t)((par * W3_ROWS + my_row) * sizeof(acc_t)), own, xbar_remote + par * 8u);
                 if constexpr (Tr::fixed) {
                     const uint32_t anybad = __any_sync(0xffffffffu, bad) ? 1u : 0u;
                     if (lane == 0) {
-                        lflag_s[par * 8 + warp] = anybad;
-                        st_async_peer(xflag_remote + (par * 8 + warp) * 4u, anybad, xbar_remote + par * 8u);
+                        lflag_s[par * G::WARPS + warp] = anybad;
+                        st_async_peer(xflag_remote + (par * G::WARPS + warp) * 4u, anybad, xbar_remote + par * 8u);
                     }
                 }
             }
@@ -617,8 +645,10 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
             {
                 const acc_t other = theirs_s[par * W3_ROWS + my_row];
                 const acc_t q = rank == 0 ? own + other : other + own;        // partial(rank 0) + partial(rank 1) on both CTAs
-                qr_s[my_row] = q;
-                if (rank == 0 && p.qr && my_row < N) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * p.N + my_row] = q;
+                if (row_owner) {
+                    qr_s[my_row] = q;
+                    if (rank == 0 && p.qr && my_row < N) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * p.N + my_row] = q;
+                }
             }
             __syncthreads();
 
@@ -649,7 +679,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                     if constexpr (Tr::fixed) {
                         uint32_t anybad = 0;
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) anybad |= lflag_s[par * 8 + k] | xflag_s[par * 8 + k];
+                        for (int k = 0; k < G::WARPS; ++k) anybad |= lflag_s[par * G::WARPS + k] | xflag_s[par * G::WARPS + k];
                         if (anybad) stw = p.constrained ? STW_INTERVAL : STW_ENGINE_RANGE;
                         const i64 rel1 = reliability_fixed(s1 / (u64)N, p, STW_SQRT_REL1, stw);
                         if (rel1 < 0 || rel1 > WSAD) stw = min(stw, STW_REL1_RANGE);
@@ -665,22 +695,24 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
             __syncthreads();
             if (!*sel_s) {
                 // exact ranking of row `tid` under (risk asc, index desc | asc): rare
-                const acc_t mineq = qr_s[tid];
-                int rk = 0;
-                for (int j = 0; j < N; ++j) {
-                    const acc_t q = qr_s[j];
-                    rk += (q < mineq) | ((q == mineq) & (high ? j > tid : j < tid));
+                if (tid < W3_ROWS) {
+                    const acc_t mineq = qr_s[tid];
+                    int rk = 0;
+                    for (int j = 0; j < N; ++j) {
+                        const acc_t q = qr_s[j];
+                        rk += (q < mineq) | ((q == mineq) & (high ? j > tid : j < tid));
+                    }
+                    const unsigned bal = __ballot_sync(0xffffffffu, tid < N && rk < R);
+                    if (lane == 0) maskw[warp] = bal;
                 }
-                const unsigned bal = __ballot_sync(0xffffffffu, tid < N && rk < R);
-                if (lane == 0) maskw[warp] = bal;
                 __syncthreads();
             }
             // every thread turns the mask bit of row `tid` into the byte forms the column units read: keep_s[row]
             // (0 / 1, exact fallbacks) and patch_s[part][value] (0x7f where dropped: OR-ed into the keys)
-            {
+            if (tid < W3_ROWS) {
                 const bool kept = (maskw[tid >> 5] >> (tid & 31)) & 1u;
                 keep_s[tid] = kept ? 1 : 0;
-                patch_s[((tid >> 1) & 3) * W3_NV + 2 * (tid >> 3) + (tid & 1)] = kept ? 0 : 0x7f;
+                patch_s[((tid & 7) / E) * NV + E * (tid >> 3) + (tid % E)] = kept ? 0 : 0x7f;
             }
             __syncthreads();                 // keep_s / patch_s are complete
             // ---- phase 4 set-up: keys of the kept rows only; the loop then runs the second-pass centre
@@ -692,13 +724,13 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                 if (refined1) {
                     // the first pass re-keyed the column: back to the first-pass scale
 #pragma unroll
-                    for (int q = 0; q < W3_NKW; ++q) kw[q] = 0u;
-                    w3_build_keys<Tr, true, FULL, false, false>(nullptr, src0, src1, kw, N, part, lo, hi, sc);
+                    for (int q = 0; q < NKW; ++q) kw[q] = 0u;
+                    w3_build_keys<Tr, P, true, FULL, false, false>(nullptr, src0, src1, kw, N, part, lo, hi, sc);
                 }
                 // dropped rows -> sentinel key (keys are <= 127, so OR-ing 0x7f gives 127)
 #pragma unroll
-                for (int q4 = 0; q4 < W3_NKW / 4; ++q4) {
-                    const uint4 d = *reinterpret_cast<const uint4 *>(patch_s + part * W3_NV + 16 * q4);
+                for (int q4 = 0; q4 < NKW / 4; ++q4) {
+                    const uint4 d = *reinterpret_cast<const uint4 *>(patch_s + part * NV + 16 * q4);
                     kw[4 * q4] |= d.x; kw[4 * q4 + 1] |= d.y; kw[4 * q4 + 2] |= d.z; kw[4 * q4 + 3] |= d.w;
                 }
             }
@@ -709,7 +741,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
         //      the kernel hung whenever another warp was last: divergent spin loops inside one warp)
         __syncwarp();
         if (lane == 0 && has_next) {
-            if (atomicAdd(done_s, 1u) == W3_THREADS / 32 - 1) {
+            if (atomicAdd(done_s, 1u) == G::WARPS - 1) {
                 *done_s = 0u;
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 mbar_expect_tx(full_bar, tile_bytes);
@@ -762,8 +794,8 @@ typedef CUresult (*W3EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, v
                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 W3EncodeFn w3_encode_fn();
 
-template <class Tr>
-int launch_wide3(const Params &p, const Plan &pl, cudaStream_t st) {
+template <class Tr, int P>
+int launch_wide3_p(const Params &p, const Plan &pl, cudaStream_t st) {
     W3EncodeFn enc = w3_encode_fn();
     if (!enc) return fail("cuTensorMapEncodeTiled is not available from this driver");
     CUtensorMap tmap;
@@ -775,15 +807,19 @@ int launch_wide3(const Params &p, const Plan &pl, cudaStream_t st) {
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return fail("cuTensorMapEncodeTiled failed with code " + std::to_string((int)cr));
-    constexpr int NCTA = w3_ctas_per_sm(sizeof(typename Tr::acc_t));
-    void (*kern)(const Params, const CUtensorMap) = (p.N == W3_ROWS) ? consensus_wide3_kernel<Tr, true, NCTA> : consensus_wide3_kernel<Tr, false, NCTA>;
+    void (*kern)(const Params, const CUtensorMap) = (p.N == W3_ROWS) ? consensus_wide3_kernel<Tr, P, true> : consensus_wide3_kernel<Tr, P, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
-    kern<<<(unsigned)pl.grid, W3_THREADS, pl.smem, st>>>(p, tmap);
+    kern<<<(unsigned)pl.grid, W3Geo<P>::THREADS, pl.smem, st>>>(p, tmap);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
     count_launch();
     return 0;
+}
+
+template <class Tr>
+int launch_wide3(const Params &p, const Plan &pl, cudaStream_t st) {
+    return pl.wP == 8 ? launch_wide3_p<Tr, 8>(p, pl, st) : launch_wide3_p<Tr, 4>(p, pl, st);
 }
 
 }  // namespace svoc

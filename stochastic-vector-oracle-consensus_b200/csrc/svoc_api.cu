@@ -134,13 +134,16 @@ static bool plan_wide3(const svoc_config &c, const void *pred, const svoc_output
     if ((long long)T * N > 0x7fffffffLL) return false;                  // TMA row coordinates are 32-bit
     pl.variant = 4;
     pl.smem = w3_smem_layout(c.dtype == SVOC_F32 ? 4 : 8).total;
-    pl.threads = W3_THREADS;
+    // lanes per column: 8 (512 threads, 64 registers, two CTAs per SM) or 4 (256 threads; three CTAs per SM for fp32)
+    static const int lanes_env = [] { const char *e = getenv("SVOC_W3_LANES"); return e ? atoi(e) : 0; }();
+    const int P = lanes_env == 4 || lanes_env == 8 ? lanes_env : W3_DEFAULT_LANES;
+    pl.threads = W3_COLS * P;
     pl.rb = 1;
     pl.npad = 0;
     pl.tile_smem = 1;
-    pl.wP = 4; pl.wRP = 64; pl.wCS = 0; pl.wH = 1;
-    // clusters of two CTAs; as many clusters as the SMs hold at once (3 CTAs per SM for fp32, 2 for the fixed form)
-    pl.grid = 2 * std::min<long long>(T, (long long)sm_count() * w3_ctas_per_sm(c.dtype == SVOC_F32 ? 4 : 8) / 2);
+    pl.wP = P; pl.wRP = W3_ROWS / P; pl.wCS = 0; pl.wH = 1;
+    // clusters of two CTAs; as many clusters as the SMs hold at once
+    pl.grid = 2 * std::min<long long>(T, (long long)sm_count() * w3_ctas_per_sm(P, c.dtype == SVOC_F32 ? 4 : 8) / 2);
     return true;
 }
 
