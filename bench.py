@@ -238,7 +238,7 @@ def c2_sweep(torch, svoc, dev, T=1_000_000):
     points = [("exact", f, 0.0) for f in (0, 1, 2)] + [("bernoulli", 2, p) for p in (0.0, 0.1, 0.2, 0.3, 0.4)]
     for mode, F, prob in points:
         gen_f = F if mode == "exact" else (0 if prob == 0.0 else 2)
-        g = svoc.generate(T, N, D, gen_f, a=10.0, b=(15.0, 30.0), failing="uniform", seed=4242, dtype=torch.float32,
+        g = svoc.generate(T, N, D, gen_f, a=(10.0, 10.0), b=(15.0, 30.0), failing="uniform", seed=4242, dtype=torch.float32,
                           device=dev, failing_prob=prob)
         run = lambda: svoc.consensus_float(g.pred, F, centre=svoc.CENTRE_MEDIAN, tie_rule=svoc.TIE_LOW_INDEX_KEPT,  # noqa: E731
                                            want_moments=False, want_qr=False, want_essence=False)

@@ -341,15 +341,32 @@ __device__ __forceinline__ void consensus_block(const Params &p, const typename 
         const val_t *cc = c1 + (size_t)r * D;
         acc_t q = 0;
         bool bad = false;
-        int d = i % D;  // rotated start: conflict-free shared-memory reads across rows
-        for (int k = 0; k < D; ++k) {
-            const in_t x = row[d];
-            if constexpr (Tr::fixed) {
+        if constexpr (Tr::fixed) {
+            int d = i % D;  // rotated start: conflict-free shared-memory reads across rows (integer sums are order-free)
+            for (int k = 0; k < D; ++k) {
+                const in_t x = row[d];
                 if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);          // math.cairo:298-310
                 else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
+                q += Tr::dev(x, cc[d]);
+                d = (d + 1 == D) ? 0 : d + 1;
             }
-            q += Tr::dev(x, cc[d]);
-            d = (d + 1 == D) ? 0 : d + 1;
+        } else {
+            // float form: EVERY row is summed in the same (natural) order, so that identical rows — colluders — get
+            // bit-identical risks and a cut inside their group is decided by the tie rule alone, as in the reference
+            // (np.linalg.norm per row, ipynb beta :358-360).  16-byte loads where the row allows it keep the
+            // shared-memory conflicts of the unrotated walk low.
+            constexpr int V = 16 / (int)sizeof(in_t);
+            if (D % V == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+                for (int d0 = 0; d0 < D; d0 += V) {
+                    const int4 raw = *reinterpret_cast<const int4 *>(row + d0);
+                    in_t xv[V];
+                    memcpy(xv, &raw, 16);
+#pragma unroll
+                    for (int k = 0; k < V; ++k) q += Tr::dev(xv[k], cc[d0 + k]);
+                }
+            } else {
+                for (int d = 0; d < D; ++d) q += Tr::dev(row[d], cc[d]);
+            }
         }
         qr_s[w] = q;
         if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)(r0 - ob) * N + w] = q;

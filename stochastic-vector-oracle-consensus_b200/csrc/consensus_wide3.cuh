@@ -66,6 +66,7 @@ struct W3Geo {
     static constexpr int MW = (NKW + 7) / 8;       // 32-bit words of a thread's row mask
     static constexpr int RT = THREADS / 16;        // rows per trip of the risk sweep (16 lanes share a row)
     static constexpr int NT = W3_ROWS / RT;        // trips
+    static constexpr int SLOTS = W3_ROWS;          // keys per column, sentinels included
 };
 
 struct W3Ctx {
@@ -81,20 +82,19 @@ __device__ __forceinline__ int w3_row(int j, int part) {
     return 8 * (j / E) + E * part + (j % E);
 }
 
-template <int P, class T>
-__device__ __forceinline__ T w3_col_sum(const W3Ctx &w, T v) {
-    constexpr int CW = W3Geo<P>::CW;
-    v += __shfl_xor_sync(w.cmask, v, CW);
-    v += __shfl_xor_sync(w.cmask, v, 2 * CW);
-    if (P == 8) v += __shfl_xor_sync(w.cmask, v, 4 * CW);
+// The lanes of a column are lane_base + CW * k, k < LANES: sums and reductions over them by xor shuffles
+template <class G, class T>
+__device__ __forceinline__ T sel_col_sum(const W3Ctx &w, T v) {
+    if (G::LANES >= 2) v += __shfl_xor_sync(w.cmask, v, G::CW);
+    if (G::LANES >= 4) v += __shfl_xor_sync(w.cmask, v, 2 * G::CW);
+    if (G::LANES >= 8) v += __shfl_xor_sync(w.cmask, v, 4 * G::CW);
     return v;
 }
-template <int P, class T, class Op>
-__device__ __forceinline__ T w3_col_reduce(const W3Ctx &w, T v, Op op) {
-    constexpr int CW = W3Geo<P>::CW;
-    v = op(v, __shfl_xor_sync(w.cmask, v, CW));
-    v = op(v, __shfl_xor_sync(w.cmask, v, 2 * CW));
-    if (P == 8) v = op(v, __shfl_xor_sync(w.cmask, v, 4 * CW));
+template <class G, class T, class Op>
+__device__ __forceinline__ T sel_col_reduce(const W3Ctx &w, T v, Op op) {
+    if (G::LANES >= 2) v = op(v, __shfl_xor_sync(w.cmask, v, G::CW));
+    if (G::LANES >= 4) v = op(v, __shfl_xor_sync(w.cmask, v, 2 * G::CW));
+    if (G::LANES >= 8) v = op(v, __shfl_xor_sync(w.cmask, v, 4 * G::CW));
     return v;
 }
 
@@ -141,40 +141,44 @@ __device__ __forceinline__ void tma_prefetch_box(const CUtensorMap *map, int col
 // the exact, slow column centre as a real call: it is reached only by degenerate columns, and inlining its
 // call sites would add a sixth to the kernel's code
 template <class Tr>
-__device__ __noinline__ typename Tr::val_t w3_exact_centre(const typename Tr::in_t *gcol, int N, const uint8_t *keep,
-                                                           int n_valid, int kind) {
+__device__ __noinline__ typename Tr::val_t sel_exact_centre(const typename Tr::in_t *gcol, int gstride, int N, const uint8_t *keep,
+                                                            int n_valid, int kind) {
     typename Tr::val_t sk, ku;
     int stw = STW_OK;
-    return column_centre_generic<Tr>(gcol, W3_D, N, keep, n_valid, kind, false, sk, ku, stw);
+    return column_centre_generic<Tr>(gcol, gstride, N, keep, n_valid, kind, false, sk, ku, stw);
 }
 
-// this thread's value j in the swizzled tile: src0 points at its first row, src1 at its second row of the same group
-// of 8 (E = 2 only; the two differ by one 128-byte line and the change of the swizzled chunk)
+// A thread's values in the swizzled tile, by value index j: src0 points at its first row, src1 at its second row of
+// the same group of 8 (E = 2 only; the two differ by one 128-byte line and the change of the swizzled chunk)
 template <int P, class in_t>
-__device__ __forceinline__ in_t w3_value(const in_t *src0, const in_t *src1, int j) {
-    constexpr int E = W3Geo<P>::E;
-    if (E == 1) return src0[j * 256];
-    return ((j & 1) ? src1 : src0)[(j >> 1) * 256];
-}
+struct W3Vals {
+    const in_t *src0, *src1;
+    int part;
+    __device__ __forceinline__ in_t operator()(int j) const {
+        constexpr int E = W3Geo<P>::E;
+        if (E == 1) return src0[j * 256];
+        return ((j & 1) ? src1 : src0)[(j >> 1) * 256];
+    }
+    __device__ __forceinline__ int row(int j) const { return w3_row<P>(j, part); }
+};
 
 // ---- keys in registers
 // FROM_REGS: the values are passed in x (first build of a round); otherwise they are read from the tile.
 // ONLY_VALID: rows whose current key is the sentinel (dropped / padded) keep it.
-template <class Tr, int P, bool FIRST, bool FULL, bool ONLY_VALID, bool FROM_REGS>
-__device__ __forceinline__ void w3_build_keys(const typename Tr::in_t *x, const typename Tr::in_t *src0, const typename Tr::in_t *src1,
-                                              unsigned (&kw)[W3Geo<P>::NKW], int N, int part,
-                                              typename Tr::in_t lo, typename Tr::in_t hi,
-                                              const typename WideKey<Tr>::Scale &sc) {
+template <class Tr, class G, bool FIRST, bool FULL, bool ONLY_VALID, bool FROM_REGS, class V>
+__device__ __forceinline__ void sel_build_keys(const typename Tr::in_t *x, const V &val, unsigned (&kw)[G::NKW], int N,
+                                               typename Tr::in_t lo, typename Tr::in_t hi,
+                                               const typename WideKey<Tr>::Scale &sc) {
 #pragma unroll
-    for (int q = 0; q < W3Geo<P>::NKW; ++q) {
+    for (int q = 0; q < G::NKW; ++q) {
         unsigned f[4];
         const unsigned old = kw[q];
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
             const int j = 4 * q + b;
-            const typename Tr::in_t xv = FROM_REGS ? x[j] : w3_value<P>(src0, src1, j);
+            const typename Tr::in_t xv = FROM_REGS ? x[j] : val(j);
             f[b] = wide_key<Tr, FIRST>(xv, lo, hi, sc);        // pack4 takes the low byte
-            if (!FULL && w3_row<P>(j, part) >= N) f[b] = 127u;
+            if (!FULL && val.row(j) >= N) f[b] = 127u;
             if (ONLY_VALID && ((old >> (8 * b)) & 0xffu) == 127u) f[b] = 127u;
         }
         kw[q] = pack4(f[0], f[1], f[2], f[3]);
@@ -215,21 +219,19 @@ template <> __device__ __forceinline__ int32_t w3_never_less<int32_t>() { return
 // kept rows in the second).  Executed by the four lanes of the column together; every one returns the result.
 // src0 / src1: this thread's rows in the tile (w3_value).  gcol / keep serve only the rare exact fallback, which
 // walks the column in global memory.  lcw: this column's candidate list (W3_LSTRIDE words).
-template <class Tr, int P, bool FULL>
-__device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const typename Tr::in_t *src0, const typename Tr::in_t *src1,
-                                                        unsigned (&kw)[W3Geo<P>::NKW],
-                                                        const typename Tr::in_t *gcol, const uint8_t *keep, int n_valid,
+template <class Tr, class G, bool FULL, class V>
+__device__ __forceinline__ typename Tr::val_t sel_centre(const W3Ctx &w, const V &val, unsigned (&kw)[G::NKW],
+                                                         const typename Tr::in_t *gcol, int gstride, const uint8_t *keep, int n_valid,
                                                         int kind, bool col_const, bool col_fallback,
                                                         typename Tr::in_t const_value, typename Tr::in_t *lcw,
                                                         bool &refined) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using Key = WideKey<Tr>;
-    using G = W3Geo<P>;
     constexpr int NKW = G::NKW, MW = G::MW;
     refined = false;
     if (col_const) return Tr::half_sum((val_t)const_value, (val_t)const_value);
-    if (col_fallback) return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
+    if (col_fallback) return sel_exact_centre<Tr>(gcol, gstride, w.N, keep, n_valid, kind);
     int klo, khi;
     centre_ranks(kind, n_valid, klo, khi);
     in_t v_lo = const_value, v_hi = const_value;
@@ -242,8 +244,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
 #pragma unroll
         for (int bit = 6; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
-            const int ge = w3_col_sum<P>(w, w3_count_ge(kw, cand, sum_keys));
-            const int lt = W3_ROWS - ge;        // sentinels (127) are never below a pivot
+            const int ge = sel_col_sum<G>(w, w3_count_ge(kw, cand, sum_keys));
+            const int lt = G::SLOTS - ge;        // sentinels (127) are never below a pivot
             if (lt <= klo) { prefix = cand; L = lt; }
             else LE = lt;                         // the last rejected pivot is prefix + 1: LE = #(key <= prefix)
         }
@@ -283,7 +285,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     bits &= bits - 1;
                     const int pos2 = bits ? __ffs(bits) - 1 : pos;       // an idle second slot re-reads the first row
                     bits &= bits - 1;
-                    const in_t xa = w3_value<P>(src0, src1, 32 * h + pos), xb = w3_value<P>(src0, src1, 32 * h + pos2);
+                    const in_t xa = val(32 * h + pos), xb = val(32 * h + pos2);
                     vmx = vmax(vmx, vmax(xa, xb));
                 }
                 bits = w2[h];
@@ -292,12 +294,12 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     bits &= bits - 1;
                     const int pos2 = bits ? __ffs(bits) - 1 : pos;
                     bits &= bits - 1;
-                    const in_t xa = w3_value<P>(src0, src1, 32 * h + pos), xb = w3_value<P>(src0, src1, 32 * h + pos2);
+                    const in_t xa = val(32 * h + pos), xb = val(32 * h + pos2);
                     vmn = vmin(vmn, vmin(xa, xb));
                 }
             }
-            v_lo = w3_col_reduce<P>(w, vmx, [](in_t a, in_t b) { return vmax(a, b); });
-            v_hi = w3_col_reduce<P>(w, vmn, [](in_t a, in_t b) { return vmin(a, b); });
+            v_lo = sel_col_reduce<G>(w, vmx, [](in_t a, in_t b) { return vmax(a, b); });
+            v_hi = sel_col_reduce<G>(w, vmn, [](in_t a, in_t b) { return vmin(a, b); });
             rescue = v_hi == w3_never_less<in_t>();
             thr = v_lo;
         } else {
@@ -311,7 +313,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 for (int h = 0; h < MW; ++h) mine += __popc(w1[h]);
                 int off = 0;
 #pragma unroll
-                for (int q = 0; q < P - 1; ++q) {
+                for (int q = 0; q < G::LANES - 1; ++q) {
                     const int cq = __shfl_sync(w.cmask, mine, w.lane_base + G::CW * q);
                     if (q < w.part) off += cq;
                 }
@@ -323,7 +325,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     while (bits) {
                         const int pos = __ffs(bits) - 1;
                         bits &= bits - 1;
-                        lcw[k++] = w3_value<P>(src0, src1, 32 * h + pos);
+                        lcw[k++] = val(32 * h + pos);
                     }
                 }
                 if (w.part == 0) {                // four sentinels behind the last candidate: the ranking reads 4 slots a trip
@@ -333,7 +335,7 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                 __syncwarp(w.cmask);
                 // rank this part's share of the slots: lt(v) = #{u < v}; rank j's value has the largest lt <= j
                 int b1 = -1, b2 = -1;
-                for (int a = w.part; a < m; a += P) {
+                for (int a = w.part; a < m; a += G::LANES) {
                     const in_t v = lcw[a];
                     int rr = 0;
 #pragma unroll 1
@@ -349,8 +351,8 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     if (rr <= j2 && code > b2) b2 = code;
                 }
                 auto imax = [](int a, int b) { return a > b ? a : b; };
-                b1 = w3_col_reduce<P>(w, b1, imax);
-                b2 = w3_col_reduce<P>(w, b2, imax);
+                b1 = sel_col_reduce<G>(w, b1, imax);
+                b2 = sel_col_reduce<G>(w, b2, imax);
                 v_lo = lcw[b1 & 0xff];
                 v_hi = lcw[b2 & 0xff];
                 __syncwarp(w.cmask);              // the list may be overwritten by the next selection
@@ -363,13 +365,13 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     while (bits) {
                         const int pos = __ffs(bits) - 1;
                         bits &= bits - 1;
-                        const uint32_t kx = okey(w3_value<P>(src0, src1, 32 * h + pos));
+                        const uint32_t kx = okey(val(32 * h + pos));
                         kmin = kx < kmin ? kx : kmin;
                         kmax = kx > kmax ? kx : kmax;
                     }
                 }
-                kmin = w3_col_reduce<P>(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
-                kmax = w3_col_reduce<P>(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
+                kmin = sel_col_reduce<G>(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+                kmax = sel_col_reduce<G>(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
                 in_t a, b;
                 unkey(kmin, a);
                 unkey(kmax, b);
@@ -378,9 +380,9 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
                     v_lo = a;
                     v_hi = a;
                 } else if (!Key::make(a, b, sc)) {
-                    return w3_exact_centre<Tr>(gcol, w.N, keep, n_valid, kind);
+                    return sel_exact_centre<Tr>(gcol, gstride, w.N, keep, n_valid, kind);
                 } else {
-                    w3_build_keys<Tr, P, false, FULL, true, false>(nullptr, src0, src1, kw, w.N, w.part, a, b, sc);
+                    sel_build_keys<Tr, G, false, FULL, true, false>(nullptr, val, kw, w.N, a, b, sc);
                     refined = true;
                     continue;
                 }
@@ -393,11 +395,11 @@ __device__ __forceinline__ typename Tr::val_t w3_centre(const W3Ctx &w, const ty
 #pragma unroll
                 for (int b = 0; b < 4; ++b) {
                     const bool valid = ((kw[q] >> (8 * b)) & 0xffu) != 127u;
-                    const in_t xv = w3_value<P>(src0, src1, 4 * q + b);
+                    const in_t xv = val(4 * q + b);
                     if (valid && xv > thr) { const uint32_t kx = okey(xv); best = kx < best ? kx : best; }
                 }
             }
-            best = w3_col_reduce<P>(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+            best = sel_col_reduce<G>(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
             unkey(best, v_hi);
         }
         break;
@@ -489,6 +491,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     const int c32 = c & 31;
     const in_t *src0 = tile_s + (c >> 5) * W3_BOX_WORDS + (E * part) * 32 + ((((c32 >> 2) ^ (E * part)) << 2) | (c32 & 3));
     const in_t *src1 = E == 1 ? src0 : tile_s + (c >> 5) * W3_BOX_WORDS + (E * part + 1) * 32 + ((((c32 >> 2) ^ (E * part + 1)) << 2) | (c32 & 3));
+    const W3Vals<P, in_t> val{src0, src1, part};
     // this thread's row unit in the risk sweep: 4-column chunk rh of row RT*t + rg (t = 0 .. NT-1); after the shuffle
     // tree the thread holds the total of row RT * (rh >> (4 - log2 NT)) + rg
     const int rh = lane & 15, rg = warp * 2 + (lane >> 4);
@@ -545,14 +548,14 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
         {
             in_t x[NV];
 #pragma unroll
-            for (int j = 0; j < NV; ++j) x[j] = w3_value<P>(src0, src1, j);
+            for (int j = 0; j < NV; ++j) x[j] = val(j);
 #pragma unroll
             for (int j = 0; j < 64 / P; ++j) {       // rows 0..63
                 lo = vmin(lo, x[j]);
                 hi = vmax(hi, x[j]);
             }
-            lo = w3_col_reduce<P>(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
-            hi = w3_col_reduce<P>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+            lo = sel_col_reduce<G>(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+            hi = sel_col_reduce<G>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
             if (!(hi > lo)) {                         // degenerate sample: exact sweep, which also detects a constant column
 #pragma unroll
                 for (int j = 0; j < NV; ++j) {
@@ -561,21 +564,21 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                         hi = vmax(hi, x[j]);
                     }
                 }
-                lo = w3_col_reduce<P>(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
-                hi = w3_col_reduce<P>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
+                lo = sel_col_reduce<G>(w, lo, [](in_t a, in_t b) { return vmin(a, b); });
+                hi = sel_col_reduce<G>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
             }
             col_const = !(hi > lo);
             col_fb = !col_const && !Key::make(lo, hi, sc);
 #pragma unroll
             for (int q = 0; q < NKW; ++q) kw[q] = 0u;
-            if (!col_const && !col_fb) w3_build_keys<Tr, P, true, FULL, false, true>(x, src0, src1, kw, N, part, lo, hi, sc);
+            if (!col_const && !col_fb) sel_build_keys<Tr, G, true, FULL, false, true>(x, val, kw, N, lo, hi, sc);
         }
         // ---- the two passes share ONE inlined copy of the centre code: pass 0 = first-pass centre, risks, row
         //      selection, key patching; pass 1 = second-pass centre
 #pragma unroll 1
         for (int pass = 0;; ++pass) {
             bool refined = false;
-            const val_t ctr = w3_centre<Tr, P, FULL>(w, src0, src1, kw, gcol, pass ? keep_s : nullptr, pass ? R : N,
+            const val_t ctr = sel_centre<Tr, G, FULL>(w, val, kw, gcol, W3_D, pass ? keep_s : nullptr, pass ? R : N,
                                                   pass ? p.centre2 : p.centre, col_const, col_fb, lo, lcw, refined);
             if (pass) {
                 if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * W3_D + gc] = ctr;
@@ -725,7 +728,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
                     // the first pass re-keyed the column: back to the first-pass scale
 #pragma unroll
                     for (int q = 0; q < NKW; ++q) kw[q] = 0u;
-                    w3_build_keys<Tr, P, true, FULL, false, false>(nullptr, src0, src1, kw, N, part, lo, hi, sc);
+                    sel_build_keys<Tr, G, true, FULL, false, false>(nullptr, val, kw, N, lo, hi, sc);
                 }
                 // dropped rows -> sentinel key (keys are <= 127, so OR-ing 0x7f gives 127)
 #pragma unroll

@@ -8,7 +8,7 @@
 #include <algorithm>
 #include <cstdlib>
 
-#include "consensus_wide3.cuh"
+#include "consensus_mid.cuh"
 #include "montecarlo.cuh"
 
 namespace svoc {
@@ -147,6 +147,30 @@ static bool plan_wide3(const svoc_config &c, const void *pred, const svoc_output
     return true;
 }
 
+// mid variant: one warp per round for 32 < N <= 64, D <= 32, 32-bit elements, median centres, no moments / rank output
+static bool plan_mid(const svoc_config &c, const svoc_outputs *out, int64_t T, Plan &pl) {
+    const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
+    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
+    if (N <= 32 || N > MID_ROWS || D < 1 || D > 32 || R < 1 || c.n_failing < 0) return false;
+    const std::string &force = forced_variant();
+    if (!force.empty() && force != "mid") return false;
+    if (c.want_moments || (out && out->rank)) return false;
+    const int centre2 = c.centre2 == SVOC_CENTRE_DEFAULT ? (c.constrained ? c.centre : SVOC_CENTRE_MEAN) : c.centre2;
+    if (c.centre == SVOC_CENTRE_MEAN || centre2 == SVOC_CENTRE_MEAN) return false;
+    const int P = D > 16 ? 1 : (D > 8 ? 2 : 4);
+    const size_t smem = mid_smem_layout(N, D, c.dtype == SVOC_F32 ? 4 : 8).total;
+    if (smem > 200 * 1024) return false;
+    pl.variant = 5;
+    pl.smem = smem;
+    pl.threads = MID_WARPS * 32;
+    pl.rb = MID_ROUNDS;
+    pl.npad = 0;
+    pl.tile_smem = 1;
+    pl.wP = P; pl.wRP = MID_ROWS / P; pl.wCS = 0; pl.wH = 1;
+    pl.grid = (T + MID_ROUNDS - 1) / MID_ROUNDS;
+    return pl.grid <= 0x7fffffffLL;
+}
+
 W3EncodeFn w3_encode_fn() {
     static W3EncodeFn fn = [] {
         void *f = nullptr;
@@ -161,6 +185,7 @@ W3EncodeFn w3_encode_fn() {
 static Plan make_plan(const svoc_config &c, const void *pred, const svoc_outputs *out, int64_t T) {
     Plan pl{};
     if (plan_wide3(c, pred, out, T, pl)) return pl;
+    if (plan_mid(c, out, T, pl)) return pl;
     if (plan_wide2(c, pred, pl)) {
         pl.grid = std::min<long long>(T, (long long)sm_count() * W2_CTAS_PER_SM);
         return pl;
@@ -337,6 +362,7 @@ const char *svoc_kernel_variant(const svoc_config *cfg) {
     const int np = svoc::npad_for(cfg->n_oracles);
     svoc::Plan pl{};
     if (svoc::plan_wide3(*cfg, nullptr, nullptr, 1, pl)) snprintf(buf, sizeof buf, "wide3");
+    else if (svoc::plan_mid(*cfg, nullptr, 1, pl)) snprintf(buf, sizeof buf, "mid");
     else if (svoc::plan_wide2(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide2");
     else if (svoc::plan_wide(*cfg, nullptr, pl)) snprintf(buf, sizeof buf, "wide");
     else if (np) snprintf(buf, sizeof buf, "small%d", np);

@@ -16,27 +16,28 @@ def shard_range(n_trials: int, rank: int, world_size: int) -> Tuple[int, int]:
     return n_trials * rank // world_size, n_trials * (rank + 1) // world_size
 
 
-def allreduce_stats(counts: torch.Tensor, sums: torch.Tensor, group=None, out=None) -> Tuple[torch.Tensor, torch.Tensor]:
-    """SUM the (int64 counts, float64 sums) accumulator pair over all ranks.
+def allreduce_stats(counts: torch.Tensor, sums: torch.Tensor, group=None, out=None):
+    """SUM the (int64 counts, float64 sums) accumulator pair over all ranks with ONE all-reduce.
 
-    The local accumulators are left untouched: they are copied into `out` (a (counts, sums) pair of the same
-    shapes, allocated once by the caller and reused every step; fresh tensors when omitted) and reduced there.
-    The two dtypes cannot share one SUM buffer without losing the exactness of the 64-bit counters (per-oracle
-    sums of wsad risks exceed 2^53 on long runs), so on NCCL both reductions are issued as ONE coalesced group
-    (a single ncclGroupStart/End, one launch); other backends (gloo in the CPU tests) get two calls."""
+    The two dtypes cannot share a SUM buffer as they are (torch's coalescing manager refuses mixed types too), and
+    the 64-bit counters must stay exact (per-oracle sums of wsad risks exceed 2^53 on long runs), so every counter
+    travels as two float64 words — its high and low 32 bits, each below 2^32 — next to the float64 sums: the sum over
+    any realistic number of ranks of such halves is exact in float64, and the halves are recombined in int64.
+    The local accumulators are left untouched.  `out` = the (counts, sums, buffer) triple a previous call returned
+    (reused, no allocation per step); returns that triple."""
     import torch.distributed as dist
+    n, m = counts.numel(), sums.numel()
     if out is None:
-        out = (torch.empty_like(counts), torch.empty_like(sums))
-    c, s = out
-    c.copy_(counts)
-    s.copy_(sums)
+        out = (torch.empty_like(counts), torch.empty_like(sums), torch.empty(2 * n + m, dtype=torch.float64, device=counts.device))
+    c, s, buf = out
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        coalesce = getattr(dist, "_coalescing_manager", None)
-        if coalesce is not None and c.is_cuda and dist.get_backend(group) == "nccl":
-            with coalesce(group=group, device=c.device, async_ops=False):
-                dist.all_reduce(c, op=dist.ReduceOp.SUM, group=group)
-                dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
-        else:
-            dist.all_reduce(c, op=dist.ReduceOp.SUM, group=group)
-            dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
-    return c, s
+        buf[:n] = counts >> 32
+        buf[n:2 * n] = counts & 0xFFFFFFFF
+        buf[2 * n:] = sums
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+        torch.add(buf[:n].to(torch.int64) << 32, buf[n:2 * n].to(torch.int64), out=c)
+        s.copy_(buf[2 * n:])
+    else:
+        c.copy_(counts)
+        s.copy_(sums)
+    return out

@@ -133,10 +133,10 @@ class RunningStats:
         from .distributed import allreduce_stats
         # the reduced copies are allocated once and reused by every later call
         self._reduced = allreduce_stats(self.counts, self.sums, group, out=self._reduced)
-        return self._reduced
+        return self._reduced[0], self._reduced[1]
 
     def summary(self, reduced: bool = False) -> dict:
-        c, s = self._reduced if (reduced and self._reduced is not None) else (self.counts, self.sums)
+        c, s = self._reduced[:2] if (reduced and self._reduced is not None) else (self.counts, self.sums)
         c, s = c.cpu(), s.cpu()
         B, H, n = _lib.STATS_COUNTS_BASE, _lib.STATS_HIST_BINS, self.n
         ok = int(c[1])

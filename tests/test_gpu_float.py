@@ -253,3 +253,32 @@ def test_row_selection_with_equal_float_images_of_integer_risks():
         assert torch.equal(a.consensus, b.consensus) and torch.equal(a.rel2, b.rel2)
         q0 = a.qr[0]
         assert int(q0.min()) > (1 << 24) and len(torch.unique(q0)) > len(torch.unique(q0.float()))
+
+
+@pytest.mark.parametrize("N,D", [(64, 16), (50, 8), (40, 32), (256, 128), (20, 4)])
+def test_identical_rows_tie_exactly_in_every_kernel(N, D):
+    """Colluders submit identical vectors: their risks must be BIT-identical (every row summed in the same order),
+    so that a cut inside the group is decided by the index rule alone — the contract keeps the higher indices
+    (sort.cairo:96-102), numpy's stable argsort the lower ones — exactly as the float64 oracle does."""
+    import svoc
+    from oracle import cref
+    rng = np.random.default_rng(seed_of("identical", N, D))
+    T, G = 200, N // 3
+    x = rng.beta(10, 15, (T, N, D))
+    pos = np.stack([rng.permutation(N)[:G] for _ in range(T)])
+    shared = np.clip(rng.beta(10, 15, (T, 1, D)) + 0.3, 0, 1)      # far from the honest rows: the group has the largest risk
+    for t in range(T):
+        x[t, pos[t]] = shared[t]
+    x = x.astype(np.float32)
+    F = G // 2                                          # the cut falls inside the group of identical rows
+    for tie in (0, 1):
+        ora = cref.float_batch(x.astype(np.float64), F, tie=tie, want_moments=False, nthreads=0)
+        r = svoc.consensus_float(torch.from_numpy(x).cuda(), F, tie_rule=tie)
+        q = r.qr.cpu().numpy()
+        for t in range(0, T, 17):
+            assert len(np.unique(q[t, pos[t]])) == 1
+        grp = ora["reliable"][np.arange(T)[:, None], pos]
+        inside = ~np.all(grp, axis=1) & np.any(grp, axis=1)
+        assert inside.mean() > 0.5                      # the test is about cuts inside the tie group
+        same = (r.reliable.cpu().numpy() == ora["reliable"]).all(axis=1)
+        assert same[inside].mean() >= 0.99, (N, D, tie, same[inside].mean())

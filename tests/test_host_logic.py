@@ -106,7 +106,8 @@ def _worker(rank, world, port, T, out):
         counts[528:535] = torch.from_numpy((~o["reliable"][ok]).sum(axis=0))
         counts[535:542] = torch.from_numpy(o["qr"][ok].sum(axis=0))
         sums[0] = float(o["rel1"][ok].sum()) * 1e-6
-        c, s = allreduce_stats(counts, sums)
+        counts[540] = (1 << 60) + 12345 + rank        # beyond 2^53: must survive the float64 transport exactly
+        c, s = allreduce_stats(counts, sums)[:2]
         if rank == 0:
             torch.save({"counts": c, "sums": s}, out)
     finally:
@@ -127,7 +128,9 @@ def test_world_size_2_allreduce_equals_single_rank(tmp_path):
     ok = o["status"] == 0
     assert int(got["counts"][0]) == T and int(got["counts"][1]) == int(ok.sum())
     assert got["counts"][528:535].tolist() == (~o["reliable"][ok]).sum(axis=0).tolist()
-    assert got["counts"][535:542].tolist() == o["qr"][ok].sum(axis=0).tolist()
+    want = o["qr"][ok].sum(axis=0).tolist()
+    assert got["counts"][535:540].tolist() == want[:5] and got["counts"][541:542].tolist() == want[6:]
+    assert int(got["counts"][540]) == 2 * ((1 << 60) + 12345) + 1
     assert abs(float(got["sums"][0]) - float(o["rel1"][ok].sum()) * 1e-6) < 1e-6
 
 
