@@ -51,6 +51,35 @@ struct WideKey<FixedTr<int32_t>> {
     }
 };
 
+// 64-bit elements: the scale is applied in double precision, the key arithmetic stays fp32 (conversion to fp32
+// rounds monotonically, and a key only has to be monotone)
+template <>
+struct WideKey<FloatTr<double>> {
+    struct Scale { double inv, off; };
+    __device__ static __forceinline__ bool make(double lo, double hi, Scale &s) {
+        s.inv = 1.0 / (hi - lo);
+        s.off = -lo * s.inv;
+        return isfinite(s.inv) && isfinite(s.off);
+    }
+    __device__ static __forceinline__ float t(double x, const Scale &s) { return __saturatef((float)fma(x, s.inv, s.off)); }
+};
+template <>
+struct WideKey<FixedTr<i64>> {
+    struct Scale { i64 lo; double inv; };
+    __device__ static __forceinline__ bool make(i64 lo, i64 hi, Scale &s) {
+        s.lo = lo;
+        s.inv = 1.0 / (double)((u64)hi - (u64)lo);
+        return true;
+    }
+    __device__ static __forceinline__ float t(i64 x, const Scale &s) {
+        return x < s.lo ? 0.0f : __saturatef((float)((double)((u64)x - (u64)s.lo) * s.inv));
+    }
+};
+
+__device__ __forceinline__ double vmin(double a, double b) { return fmin(a, b); }
+__device__ __forceinline__ double vmax(double a, double b) { return fmax(a, b); }
+__device__ __forceinline__ i64 vmin(i64 a, i64 b) { return a < b ? a : b; }
+__device__ __forceinline__ i64 vmax(i64 a, i64 b) { return a > b ? a : b; }
 __device__ __forceinline__ float vmin(float a, float b) { return fminf(a, b); }
 __device__ __forceinline__ float vmax(float a, float b) { return fmaxf(a, b); }
 __device__ __forceinline__ int32_t vmin(int32_t a, int32_t b) { return min(a, b); }

@@ -28,6 +28,9 @@ namespace svoc {
 #endif
 constexpr int W2_THREADS = W2_THREADS_N;
 constexpr int W2_CTAS_PER_SM = 1024 / W2_THREADS;
+// 64-bit elements: one CTA per SM (128 registers) — at 64 registers the double / int64 arithmetic spills
+template <class Tr>
+constexpr int w2_ctas_per_sm() { return sizeof(typename Tr::in_t) == 8 ? 1 : W2_CTAS_PER_SM; }
 #ifndef W2_CAP_N
 #define W2_CAP_N 32
 #endif
@@ -103,6 +106,12 @@ __device__ __forceinline__ void w2_build_keys(const W2Ctx &w, const typename Tr:
 __device__ __forceinline__ void count_lt(int &r, float u, float v) {
     asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(r) : "f"(u), "f"(v));
 }
+__device__ __forceinline__ void count_lt(int &r, double u, double v) {
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.f64 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(r) : "d"(u), "d"(v));
+}
+__device__ __forceinline__ void count_lt(int &r, i64 u, i64 v) {
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.s64 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(r) : "l"(u), "l"(v));
+}
 __device__ __forceinline__ void count_lt(int &r, int32_t u, int32_t v) {
     asm("{\n\t.reg .pred p;\n\tsetp.lt.s32 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(r) : "r"(u), "r"(v));
 }
@@ -117,6 +126,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using Key = WideKey<Tr>;
+    using key_t = decltype(okey(in_t()));          // order-preserving unsigned image of an element
     const int WD = DT ? DT : w.D;
     const int WP = PT ? PT : P_rt;
     const int WRP = RPT ? RPT : w.RP;
@@ -194,7 +204,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
         const int j1 = klo - L, j2 = khi - L;
         bool rescue = false;
         in_t thr = const_value;
-        uint32_t kmin = 0xffffffffu, kmax = 0u;
+        key_t kmin = ~key_t(0), kmax = 0;
         if (m <= W2_CAP) {
             // values of this part's window rows -> slots off..  W2_CHUNK loads are issued before the first value is
             // stored (W2_CHUNK = 2 measured best: 1 serialises the round trips, 4 spends too many idle slots)
@@ -262,13 +272,13 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
                 while (acc) {
                     const int pos = __ffs(acc) - 1;
                     acc &= acc - 1;
-                    const uint32_t kx = okey(tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c]);
+                    const key_t kx = okey(tile[(row_lo + g + 4 * (7 - (pos & 7)) + (pos >> 3)) * WD + w.c]);
                     kmin = kx < kmin ? kx : kmin;
                     kmax = kx > kmax ? kx : kmax;
                 }
             }
-            kmin = col_reduce(w, kmin, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
-            kmax = col_reduce(w, kmax, [](uint32_t a, uint32_t b) { return a > b ? a : b; });
+            kmin = col_reduce(w, kmin, [](key_t a, key_t b) { return a < b ? a : b; });
+            kmax = col_reduce(w, kmax, [](key_t a, key_t b) { return a > b ? a : b; });
             in_t a, b;
             unkey(kmin, a);
             unkey(kmax, b);
@@ -291,7 +301,7 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
         if (rescue) {                             // rank khi lies above the window: smallest flagged value above it
             // sixteen independent loads per trip (the flags are applied afterwards): a dependent chain of 64
             // L2 round trips here would hold the whole CTA at its next barrier
-            uint32_t best = 0xffffffffu;
+            key_t best = ~key_t(0);
             const in_t *ptr = tile + row_lo * WD + w.c;
             for (int row = row_lo; row < row_hi; row += 16, ptr += 16 * WD) {
                 in_t x[16];
@@ -303,10 +313,10 @@ __device__ __forceinline__ typename Tr::val_t w2_centre(const W2Ctx &w, const ty
 #pragma unroll
                 for (int k = 0; k < 16; ++k) {
                     const bool on = (kw4[k >> 2] >> (8 * (k & 3))) & 0xffu;
-                    if (on && x[k] > thr) { const uint32_t kx = okey(x[k]); best = kx < best ? kx : best; }
+                    if (on && x[k] > thr) { const key_t kx = okey(x[k]); best = kx < best ? kx : best; }
                 }
             }
-            best = col_reduce(w, best, [](uint32_t a, uint32_t b) { return a < b ? a : b; });
+            best = col_reduce(w, best, [](key_t a, key_t b) { return a < b ? a : b; });
             unkey(best, v_hi);
         }
         break;
@@ -356,8 +366,8 @@ __device__ __forceinline__ bool w2_select_rows(const acc_t (&q)[NS], int N, int 
         bmax = __reduce_max_sync(full, bmax);
         if (bmax >= 0x7f800000u) return false;       // sign bit, inf, nan: non-negative finite floats order like their bits
         if (bmax == bmin) {
-            if constexpr (!std::is_floating_point<acc_t>::value) {
-                // equal images need not be equal integers: check
+            if constexpr (!std::is_same<acc_t, float>::value) {
+                // equal fp32 images need not be equal 64-bit risks (integers or doubles): check
                 const unsigned first = __ballot_sync(full, cand != 0);
                 acc_t ref = 0;
 #pragma unroll
@@ -465,7 +475,7 @@ __device__ __forceinline__ bool w2_select_rows(const acc_t (&q)[NS], int N, int 
 }
 
 template <class Tr, int DT, int PT, int RPT>
-__global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_kernel(const Params p) {
+__global__ void __launch_bounds__(W2_THREADS, w2_ctas_per_sm<Tr>()) consensus_wide2_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     using acc_t = typename Tr::acc_t;
@@ -584,14 +594,17 @@ __global__ void __launch_bounds__(W2_THREADS, W2_CTAS_PER_SM) consensus_wide2_ke
                     val_t cc[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) cc[k] = c1[d + k];
-                    int4 xv[4];
+                    constexpr int NQ = sizeof(in_t) / 4;          // 16-byte loads per 4 elements
+                    int4 xv[4][NQ];
 #pragma unroll
                     for (int u = 0; u < 4; ++u)
-                        xv[u] = (i0 + u < N) ? *reinterpret_cast<const int4 *>(rp + u * D) : make_int4(0, 0, 0, 0);
+#pragma unroll
+                        for (int h = 0; h < NQ; ++h)
+                            xv[u][h] = (i0 + u < N) ? reinterpret_cast<const int4 *>(rp + u * D)[h] : make_int4(0, 0, 0, 0);
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         in_t x[4];
-                        memcpy(x, &xv[u], 16);
+                        memcpy(x, &xv[u][0], 4 * sizeof(in_t));
                         if (i0 + u < N) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k) {
@@ -873,7 +886,7 @@ int launch_wide2(const Params &p, const Plan &pl, cudaStream_t st) {
     void (*kern)(const Params) = consensus_wide2_kernel<Tr, 0, 0, 0>;
 #if W2_THREADS_N == 512
     if (p.D == 128 && p.wP == 4 && p.wRP == 64) kern = consensus_wide2_kernel<Tr, 128, 4, 64>;
-    else if (p.D == 128 && p.wP == 4) kern = consensus_wide2_kernel<Tr, 128, 4, 0>;
+    else if (sizeof(typename Tr::in_t) == 4 && p.D == 128 && p.wP == 4) kern = consensus_wide2_kernel<Tr, 128, 4, 0>;
 #else
     if (p.D == 128 && p.wP == 2 && p.wRP == 128) kern = consensus_wide2_kernel<Tr, 128, 2, 128>;
 #endif

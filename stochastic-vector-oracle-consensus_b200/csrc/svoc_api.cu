@@ -89,11 +89,11 @@ static const std::string &forced_variant() {
 // wide2 variant: parts of a column inside one warp, the round read from global memory / L2 (two CTAs per SM)
 static bool plan_wide2(const svoc_config &c, const void *pred, Plan &pl) {
     const int N = c.n_oracles, D = c.dimension, R = c.n_oracles - c.n_failing;
-    if (!(c.dtype == SVOC_F32 || c.dtype == SVOC_I32)) return false;
     if (N <= 64 || N > 512 || D > 512 || R < 2 || c.n_failing < 0) return false;
     const std::string &force = forced_variant();
     if (!force.empty() && force != "wide2") return false;
-    const size_t round_bytes = (size_t)N * D * 4;
+    const size_t es = elem_size(c.dtype);            // 64-bit elements too: keys and counting are type-independent
+    const size_t round_bytes = (size_t)N * D * es;
     if ((reinterpret_cast<uintptr_t>(pred) & 15) != 0 || (round_bytes & 15) != 0) return false;
     int P = 1;
     while (P * 2 <= 8 && P * 2 * D <= W2_THREADS && P * 2 * 32 <= N) P *= 2;
@@ -106,7 +106,7 @@ static bool plan_wide2(const svoc_config &c, const void *pred, Plan &pl) {
     int HR = 1;
     while (HR * 2 <= 4 && HR * 2 * N <= W2_THREADS && D / (HR * 2) >= 8) HR *= 2;
     if ((W2_THREADS / 32) * (32 / HR) < 1) return false;
-    const size_t smem = wide2_smem_bytes(N, D, P, RP, CS, 4, c.dtype == SVOC_F32 ? 4 : 8);
+    const size_t smem = wide2_smem_bytes(N, D, P, RP, CS, es, c.dtype == SVOC_F32 ? 4 : 8);
     if (smem > 110 * 1024) return false;
     pl.variant = 3;
     pl.wP = P; pl.wRP = RP; pl.wCS = CS; pl.wH = HR;
@@ -187,7 +187,7 @@ static Plan make_plan(const svoc_config &c, const void *pred, const svoc_outputs
     if (plan_wide3(c, pred, out, T, pl)) return pl;
     if (plan_mid(c, out, T, pl)) return pl;
     if (plan_wide2(c, pred, pl)) {
-        pl.grid = std::min<long long>(T, (long long)sm_count() * W2_CTAS_PER_SM);
+        pl.grid = std::min<long long>(T, (long long)sm_count() * (elem_size(c.dtype) == 8 ? 1 : W2_CTAS_PER_SM));
         return pl;
     }
     if (forced_variant() != "generic" && plan_wide(c, pred, pl)) {

@@ -105,9 +105,14 @@ class RunningStats:
     """Accumulators over many rounds: status counts, rel1/rel2 histograms (256 bins over [0, 1]),
     per-oracle "not reliable" counts and per-oracle sum of quadratic risk."""
 
-    def __init__(self, n_oracles: int, device=None):
+    def __init__(self, n_oracles: int, device=None, window: int = 0):
+        """window = k > 0 also keeps the reliable flags of the LAST k accepted rounds (status 0) in a ring, for the
+        "recently unreliable" rule of a replacement proposal; 0 keeps the running totals only."""
         self.n = int(n_oracles)
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.window = int(window)
+        self._ring = None              # [k, ceil(N/32)] int32 reliable words of the last k accepted rounds, oldest first
+        self._ring_len = 0
         self.counts = torch.zeros(_lib.STATS_COUNTS_BASE + 2 * self.n + _lib.MC_EXTRA, dtype=torch.int64, device=self.device)
         self.sums = torch.zeros(_lib.STATS_SUMS_BASE + self.n + _lib.MC_EXTRA, dtype=torch.float64, device=self.device)
         self._reduced = None
@@ -126,6 +131,36 @@ class RunningStats:
             st = torch.cuda.current_stream().cuda_stream
             _lib.check(_lib.load().svoc_accumulate_stats(C.byref(cfg), T, C.byref(outs), C.c_void_p(self.counts.data_ptr()),
                                                          C.c_void_p(self.sums.data_ptr()), C.c_void_p(st)))
+        if self.window > 0:
+            self._push_window(res)
+
+    def _push_window(self, res: ConsensusResult) -> None:
+        """Append the accepted rounds of `res` (status 0, in batch order) to the ring and keep its last k entries.
+        Only the tail of the batch can survive, so at most k rounds are gathered."""
+        k = self.window
+        ok = torch.nonzero(res.status == 0).flatten()
+        if ok.numel() == 0:
+            return
+        new = res.reliable_words.index_select(0, ok[-k:])
+        old = self._ring[: self._ring_len] if self._ring is not None else new[:0]
+        both = torch.cat([old, new], dim=0)[-k:]
+        if self._ring is None:
+            self._ring = torch.zeros((k, new.shape[1]), dtype=new.dtype, device=new.device)
+        self._ring_len = both.shape[0]
+        self._ring[: self._ring_len] = both
+
+    def window_unreliable_counts(self) -> torch.Tensor:
+        """[N] int64: in how many of the last k accepted rounds each oracle was NOT reliable (OracleInfo.reliable
+        false, contract.cairo:345-363)."""
+        out = torch.zeros(self.n, dtype=torch.int64, device=self.device)
+        if self._ring is None or self._ring_len == 0:
+            return out
+        idx = torch.arange(self.n, device=self.device)
+        bits = (self._ring[: self._ring_len][:, idx // 32] >> (idx % 32)) & 1
+        return self._ring_len - bits.sum(dim=0).to(torch.int64)
+
+    def window_rounds(self) -> int:
+        return self._ring_len
 
     def allreduce(self, group=None):
         """SUM the local accumulators over all ranks (NCCL over NVLink on GPUs); returns (counts, sums)
@@ -167,11 +202,17 @@ class RunningStats:
         B = _lib.STATS_COUNTS_BASE
         return self.counts[B + self.n:B + 2 * self.n] if fixed else self.sums[_lib.STATS_SUMS_BASE:_lib.STATS_SUMS_BASE + self.n]
 
-    def replacement_candidates(self, min_fraction: float = 0.5) -> list:
-        """Oracles flagged unreliable in at least `min_fraction` of the accepted rounds — the indices an
-        admin would put in `update_proposition` (contract.cairo:661-717)."""
-        ok = int(self.counts[1])
-        if ok == 0:
+    def replacement_candidates(self, min_fraction: float = 0.5, recent: bool = False) -> list:
+        """Oracles flagged unreliable in at least `min_fraction` of the accepted rounds — of all rounds seen, or
+        (recent=True) of the last-k window — most often flagged first: the indices an admin would put in
+        `update_proposition` (contract.cairo:661-717; documentation/README.md:152-175 leaves the rule to the admins)."""
+        if recent:
+            total, counts = self.window_rounds(), self.window_unreliable_counts()
+        else:
+            total, counts = int(self.counts[1]), self.unreliable_counts()
+        if total == 0:
             return []
-        frac = self.unreliable_counts().double() / ok
-        return torch.nonzero(frac >= min_fraction).flatten().tolist()
+        frac = counts.double() / total
+        hit = torch.nonzero(frac >= min_fraction).flatten()
+        order = torch.argsort(frac[hit], descending=True, stable=True)
+        return hit[order].tolist()

@@ -93,6 +93,31 @@ def test_config4_bulk_fixed_point_vs_oracle():
     assert np.array_equal(r.rel1.cpu().numpy(), ora["rel1"]) and np.array_equal(r.reliable.cpu().numpy(), ora["reliable"])
 
 
+def test_config4_shape_in_float64_and_int64():
+    """N > 64 in the 64-bit element types — the reference's own float precision (np.median on float64, ipynb beta
+    :354-371; the 1e-6 tolerance is stated for it) and unconstrained int64 contract values (contract.cairo:370-434) —
+    run the wide2 kernel too: 10 000 rounds of the config-4 shape against the oracle."""
+    import svoc
+    from oracle import cref
+    T, N, D, F = 10_000, 256, 128, 51
+    assert svoc.kernel_variant(N, D, torch.float64) == "wide2"
+    g = svoc.generate(T, N, D, F, a=10.0, b=15.0, failing="colluding", shift=0.15, seed=99, dtype=torch.float64)
+    xd = g.pred.cpu().numpy()
+    for centre, tie in ((1, 1), (0, 0)):
+        ora = cref.float_batch(xd, F, centre=centre, tie=tie, want_moments=False, nthreads=0)
+        r = _np_result(svoc.consensus_float(g.pred, F, centre=centre, tie_rule=tie, want_moments=False), N)
+        _float_compare(r, ora, N, F, torch.float64, f"c4 shape fp64 centre={centre}", 0.9999, True)
+    gi = svoc.generate(3000, N, D, F, a=10.0, b=15.0, failing="colluding", shift=0.15, seed=98, dtype=torch.int64)
+    xi = gi.pred.cpu().numpy()
+    ora = cref.fixed_batch(xi, F, True, 0, True, nthreads=0)
+    r = result_to_numpy(svoc.consensus_fixed(gi.pred, F, want_moments=True))
+    assert_fixed_equal(r, ora, 3000, label="c4 shape int64")
+    wide = (xi.astype(np.int64) - 500_000) * 37 + 20_000_000          # unconstrained values around 20 +- 18 (wsad)
+    ora = cref.fixed_batch(wide, F, False, 10 * W, False, nthreads=0)
+    r = result_to_numpy(svoc.consensus_fixed(torch.from_numpy(wide).cuda(), F, constrained=False, max_spread=10 * W, want_moments=False))
+    assert_fixed_equal(r, ora, 3000, want_moments=False, label="c4 shape int64 unconstrained")
+
+
 # ------------------------------------------------------------------------------------------ config 3
 def _c3_rounds(T, N, D, F, seed):
     """bench.py's config-3 draw (int32 wsad, beta(10,15) honest, F uniform failing) with blocks of rounds replaced

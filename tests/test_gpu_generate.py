@@ -180,3 +180,66 @@ def test_bernoulli_failing_mode():
     assert torch.all((~g0.honest).sum(dim=1) == 2)
     with pytest.raises(RuntimeError):
         svoc.generate(10, N, D, 2, failing_prob=1.5)
+
+
+def test_replacement_candidates_and_last_k_window_match_numpy():
+    """running per-oracle "not reliable" counts, the last-k window and the proposal rule, against a
+    numpy restatement on the same per-round flags (OracleInfo.reliable, contract.cairo:345-363)."""
+    import svoc
+    N, D, F, k = 16, 4, 3, 500
+    g = svoc.generate(6000, N, D, F, a=10, b=15, seed=31, dtype=torch.int32)
+    x = g.pred.clone()
+    x[:, 5, :] = torch.randint(0, 1_000_000, (6000, D), device=x.device, dtype=torch.int32)    # oracle 5 always noisy
+    x[4000:, 9, :] = 990_000                                                                     # oracle 9 breaks late
+    x[::13, 0, 0] = 2_000_000                                                                    # some rounds revert
+    st = svoc.RunningStats(N, window=k)
+    chunks = [x[:2500], x[2500:2501], x[2501:5200], x[5200:]]        # uneven batches, one of a single round
+    masks, status = [], []
+    for c in chunks:
+        r = svoc.consensus_fixed(c, F, want_moments=False)
+        st.update(r)
+        masks.append(r.reliable.cpu().numpy())
+        status.append(r.status.cpu().numpy())
+    masks, status = np.concatenate(masks), np.concatenate(status)
+    ok = status == 0
+    unrel = ~masks[ok]
+    assert np.array_equal(st.unreliable_counts().cpu().numpy(), unrel.sum(axis=0))
+    assert st.window_rounds() == k
+    assert np.array_equal(st.window_unreliable_counts().cpu().numpy(), unrel[-k:].sum(axis=0))
+    frac = unrel.mean(axis=0)
+    want = [i for i in np.argsort(-frac, kind="stable") if frac[i] >= 0.5]
+    assert st.replacement_candidates(0.5) == want and want[0] == 5 and 9 not in want
+    frac_k = unrel[-k:].mean(axis=0)
+    want_k = [i for i in np.argsort(-frac_k, kind="stable") if frac_k[i] >= 0.5]
+    assert st.replacement_candidates(0.5, recent=True) == want_k and 9 in want_k and 5 in want_k
+    small = svoc.RunningStats(N, window=k)
+    small.update(svoc.consensus_fixed(x[:40], F, want_moments=False))     # fewer accepted rounds than the window holds
+    assert small.window_rounds() == int((status[:40] == 0).sum())
+
+
+def test_rounds_to_proposal_to_vote_to_replacement():
+    """End to end over f1: consensus rounds -> RunningStats -> replacement candidate -> update_proposition -> votes
+    of the admins -> the oracle's address is swapped and the vote state reset (contract.cairo:547-580, 661-738)."""
+    import svoc
+    from svoc.contract import OracleConsensusNDS
+    N, D, F = 7, 2, 2
+    g = svoc.generate(4000, N, D, F, a=10, b=15, seed=77, dtype=torch.int32)
+    x = g.pred.clone()
+    x[:, 3, :] = torch.randint(0, 1_000_000, (4000, D), device=x.device, dtype=torch.int32)     # oracle 3 is dead: pure noise
+    st = svoc.RunningStats(N, window=1000)
+    st.update(svoc.consensus_fixed(x, F, want_moments=False))
+    cands = st.replacement_candidates(0.5, recent=True)
+    assert cands and cands[0] == 3
+    admins, oracles = ["Akashi", "Ozu", "Higuchi"], [f"oracle_{i:02d}" for i in range(N)]
+    c = OracleConsensusNDS(admins, True, 2, F, True, 0, D, oracles)
+    c.set_caller(admins[0])
+    c.update_proposition((cands[0], "oracle_new"))           # the proposer votes for itself
+    assert c.get_oracle_list()[3] == "oracle_03"
+    c.set_caller(admins[1])
+    c.vote_for_a_proposition(0, True)                        # second vote: the required majority of 2 is reached
+    assert c.get_oracle_list()[3] == "oracle_new"
+    assert c.get_replacement_propositions() == [None] * 3 and not any(any(v) for v in c.vote_matrix)
+    # the replaced oracle commits under its new address
+    c.set_caller("oracle_new")
+    c.update_prediction([400000, 300000])
+    assert c.n_active_oracles == 1
