@@ -35,15 +35,22 @@ struct MidGeo {
     static constexpr int NKW = NV / 4;
     static constexpr int MW = (NKW + 7) / 8;
     static constexpr int SLOTS = MID_ROWS;
+    // 64 values per column: 6-bit keys (about two values per bucket near the median) and the next FOUR buckets searched
+    // for the value above the median.  With 7 bits most buckets are empty and the scan over all values that replaces an
+    // empty window ran in nearly every warp; with 5 bits the buckets held 4-5 values and their exact ranking cost as
+    // much as the sorting network this kernel replaces (profiles/r02h, r02j).
+    static constexpr int KBITS = 6;
+    static constexpr int NEXT = 4;
 };
 
-// a lane's values of its column in the staged round: rows P*j + part
-template <int P, class in_t>
+// a lane's values of its column in the staged round: rows P*j + part.  STRIDE = P * D when that is a compile-time
+// constant (D = 32 / P: every load then has an immediate offset), 0 = run-time stride
+template <int P, int STRIDE, class in_t>
 struct MidVals {
     const in_t *base;        // tile + part * D + column
     int stride;              // P * D
     int part;
-    __device__ __forceinline__ in_t operator()(int j) const { return base[j * stride]; }
+    __device__ __forceinline__ in_t operator()(int j) const { return base[j * (STRIDE ? STRIDE : stride)]; }
     __device__ __forceinline__ int row(int j) const { return P * j + part; }
 };
 
@@ -66,12 +73,13 @@ __host__ __device__ inline MidSmem mid_smem_layout(int N, int D, size_t vs) {
     s.sum1 = take((size_t)MID_ROUNDS * vs, 16);
     s.sum2 = take((size_t)MID_ROUNDS * vs, 16);
     s.stw = take((size_t)MID_ROUNDS * 4, 16);
-    s.bar = take(16, 16);
+    s.bar = take(8 * MID_WARPS, 16);
     s.total = off;
     return s;
 }
 
-template <class Tr, int P, bool FULL>
+// DEXACT: D == 32 / P exactly (config 3: D = 16, P = 2) — strides and the risk walk are compile-time then
+template <class Tr, int P, bool FULL, bool DEXACT>
 __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const Params p) {
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
@@ -80,7 +88,7 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
     using G = MidGeo<P>;
     constexpr int NV = G::NV, NKW = G::NKW, CW = G::CW;
     extern __shared__ __align__(128) unsigned char smem_mid[];
-    const int N = FULL ? MID_ROWS : p.N, D = p.D, R = p.R;
+    const int N = FULL ? MID_ROWS : p.N, D = DEXACT ? CW : p.D, R = p.R;
     const MidSmem S = mid_smem_layout(p.N, D, sizeof(acc_t));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t round_elems = (size_t)p.N * D;
@@ -119,36 +127,43 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
     const int rot = (32 % D == 0) ? lane / (32 / D) : lane;            // per-lane rotation of the risk walk
 
     for (int k = tid; k < MID_ROUNDS; k += blockDim.x) stw_s[k] = STW_OK;
-    if (tid == 0) mbar_init(bar, 1);
+    if (tid < MID_WARPS) mbar_init(bar + tid, 1);
     __syncthreads();
 
-    uint32_t phase = 0;                                                // completed bulk copies
+    // Every warp stages its OWN rounds (one TMA bulk copy per round into the warp's slot of the tile, completing on the
+    // warp's mbarrier) and issues the copy of its next round as soon as it has finished the current one: no CTA-wide
+    // barrier inside the loop, and the copy's latency is covered by the other warps of the SM.
+    const in_t *g_first = reinterpret_cast<const in_t *>(p.pred) + (size_t)r_first * round_elems;
+    const uint32_t rbytes = (uint32_t)(round_elems * sizeof(in_t));
+    const bool bulk = ((reinterpret_cast<uintptr_t>(g_first) & 15) == 0) && ((rbytes & 15) == 0);
+    in_t *tile = tile_s + (size_t)warp * round_elems;
+    auto stage = [&](int slot) {          // this warp's round `slot` -> its tile slot
+        const in_t *src = g_first + (size_t)slot * round_elems;
+        if (bulk) {
+            if (lane == 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(bar + warp, rbytes);
+                bulk_g2s(tile, src, rbytes, bar + warp);
+            }
+        } else {
+            for (int e = lane; e < (int)round_elems; e += 32) tile[e] = src[e];
+        }
+    };
+    if (warp < n_here) stage(warp);
+    uint32_t phase = 0;
     for (int it = 0; it * MID_WARPS < n_here; ++it) {
         const int nr = min(MID_WARPS, n_here - it * MID_WARPS);         // rounds of this batch
-        const in_t *gsrc = reinterpret_cast<const in_t *>(p.pred) + (size_t)(r_first + it * MID_WARPS) * round_elems;
-        // ---- stage the batch: one TMA bulk copy when the source is 16-byte aligned
-        const size_t bytes = (size_t)nr * round_elems * sizeof(in_t);
-        const bool bulk = ((reinterpret_cast<uintptr_t>(gsrc) & 15) == 0) && ((bytes & 15) == 0);
-        if (bulk) {
-            if (tid == 0) {
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_expect_tx(bar, (uint32_t)bytes);
-                bulk_g2s(tile_s, gsrc, (uint32_t)bytes, bar);
-            }
-            mbar_wait(bar, phase & 1u);
-            ++phase;
-        } else {
-            for (size_t e = tid; e < (size_t)nr * round_elems; e += blockDim.x) tile_s[e] = gsrc[e];
-            __syncthreads();
-        }
+        const in_t *gsrc = g_first + (size_t)(it * MID_WARPS) * round_elems;
         if (warp < nr) {
             const int slot = it * MID_WARPS + warp;
             const i64 r = r_first + slot;
-            const in_t *tile = tile_s + (size_t)warp * round_elems;
+            if (bulk) mbar_wait(bar + warp, phase & 1u);
+            ++phase;
+            __syncwarp();
             const in_t *gcol = gsrc + (size_t)warp * round_elems + cq;
-            const MidVals<P, in_t> val{tile + part * D + cq, P * D, part};
+            const MidVals<P, DEXACT ? 32 : 0, in_t> val{tile + part * D + cq, P * D, part};
             // ---- first-pass centre of the lane's column
-            bool col_const = false, col_fb = false, refined1 = false;
+            bool col_const = false, col_fb = false, refined1 = false, bad = false;
             in_t lo = std::numeric_limits<in_t>::max(), hi = std::numeric_limits<in_t>::lowest();
             typename Key::Scale sc{};
             unsigned kw[NKW];
@@ -169,6 +184,10 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
                 hi = sel_col_reduce<G>(w, hi, [](in_t a, in_t b) { return vmax(a, b); });
                 col_const = !(hi > lo);
                 col_fb = !col_const && !Key::make(lo, hi, sc);
+                if constexpr (Tr::fixed) {          // the interval check (math.cairo:298-310) on the column's extremes
+                    if (p.constrained) bad = (lo < 0) | ((i64)hi > WSAD);
+                    else bad = ((i64)hi > ENGINE_RANGE) | ((i64)lo < -ENGINE_RANGE);
+                }
                 if (!col_const && !col_fb) sel_build_keys<Tr, G, true, FULL, false, true>(x, val, kw, N, lo, hi, sc);
                 const val_t e1 = sel_centre<Tr, G, FULL>(w, val, kw, gcol, D, nullptr, N, p.centre, col_const, col_fb, lo, lcw, refined1);
                 if (part == 0) {
@@ -182,7 +201,6 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
             //      rows must get bit-identical risks (colluders tie exactly, and the tie rule decides), so every row is
             //      summed in the SAME order: column-wise, (x - e1)^2 of the lane's own column folded over the column
             //      lanes by a transposing shuffle tree, which leaves lane cq with values 2cq, 2cq + 1 of its part.
-            bool bad = false;
             if constexpr (Tr::fixed) {
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -190,13 +208,31 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
                     if (row < N) {
                         const in_t *xr = tile + (size_t)row * D;
                         acc_t q = 0;
-                        int dd = rot % D;
-                        for (int k = 0; k < D; ++k) {
-                            const in_t x = xr[dd];
-                            if (p.constrained) bad |= (x < 0) | ((i64)x > WSAD);
-                            else bad |= ((i64)x > ENGINE_RANGE) | ((i64)x < -ENGINE_RANGE);
-                            q += Tr::dev(x, c1_w[dd]);
-                            dd = (dd + 1 == D) ? 0 : dd + 1;
+                        if (p.constrained) {
+                            // |x - centre| <= 1e6: 32-bit squares (wmul_sq_small), 32-bit sum (at most 32 * 1 000 001)
+                            uint32_t q32 = 0;
+                            if (DEXACT) {
+#pragma unroll
+                                for (int k = 0; k < CW; ++k) {
+                                    const int dd = (rot + k) & (CW - 1);
+                                    const int diff = (int)xr[dd] - (int)c1_w[dd];
+                                    q32 += wmul_sq_small((uint32_t)(diff < 0 ? -diff : diff));
+                                }
+                            } else {
+                                int dd = rot % D;
+                                for (int k = 0; k < D; ++k) {
+                                    const int diff = (int)xr[dd] - (int)c1_w[dd];
+                                    q32 += wmul_sq_small((uint32_t)(diff < 0 ? -diff : diff));
+                                    dd = (dd + 1 == D) ? 0 : dd + 1;
+                                }
+                            }
+                            q = q32;
+                        } else {
+                            int dd = rot % D;
+                            for (int k = 0; k < D; ++k) {
+                                q += Tr::dev(xr[dd], c1_w[dd]);
+                                dd = (dd + 1 == D) ? 0 : dd + 1;
+                            }
                         }
                         qr_w[row] = q;
                         if (p.qr) reinterpret_cast<acc_t *>(p.qr)[(size_t)r * p.N + row] = q;
@@ -287,9 +323,11 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
                 }
                 if (part == 0) reinterpret_cast<val_t *>(p.consensus)[(size_t)r * D + cq] = cons;
             }
+            __syncwarp();             // every lane has made its last read of the slot
+            if (slot + MID_WARPS < n_here) stage(slot + MID_WARPS);
         }
-        __syncthreads();          // the tile is free for the next batch
     }
+    __syncthreads();
 
     // ---- the reliabilities of the CTA's rounds, one task (round, pass) per thread: two Newton square roots per round
     for (int task = tid; task < 2 * n_here; task += blockDim.x) {
@@ -324,7 +362,9 @@ __global__ void __launch_bounds__(MID_WARPS * 32, 3) consensus_mid_kernel(const 
 
 template <class Tr, int P>
 int launch_mid_p(const Params &p, const Plan &pl, cudaStream_t st) {
-    void (*kern)(const Params) = (p.N == MID_ROWS) ? consensus_mid_kernel<Tr, P, true> : consensus_mid_kernel<Tr, P, false>;
+    const bool dexact = p.D == 32 / P;
+    void (*kern)(const Params) = (p.N == MID_ROWS) ? (dexact ? consensus_mid_kernel<Tr, P, true, true> : consensus_mid_kernel<Tr, P, true, false>)
+                                                   : (dexact ? consensus_mid_kernel<Tr, P, false, true> : consensus_mid_kernel<Tr, P, false, false>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
     kern<<<(unsigned)pl.grid, MID_WARPS * 32, pl.smem, st>>>(p);

@@ -169,13 +169,14 @@ struct WideCtx {
 
 // 7-bit key of one element.  Level 0: the scale spans the column's exact [min, max] and keys use
 // 0..126.  Refinement levels: the scale spans a sub-range; 0 = below it, 126 = above it, 1..125 inside.
-template <class Tr, bool FIRST>
+// KTOP = the largest key (126 for 7-bit keys; the mid kernel's 64-row columns use 5-bit keys, KTOP = 30).
+template <class Tr, bool FIRST, int KTOP = 126>
 __device__ __forceinline__ unsigned wide_key(typename Tr::in_t x, typename Tr::in_t lo, typename Tr::in_t hi,
                                              const typename WideKey<Tr>::Scale &sc) {
     const float t = WideKey<Tr>::t(x, sc);
-    if (FIRST) return __float_as_uint(__fmaf_rn(t, 126.0f, 8388608.0f));
-    const unsigned k = __float_as_uint(__fmaf_rn(t, 124.0f, 8388609.0f));   // 1 + round(124 t) in the low byte
-    return x < lo ? 0u : (x > hi ? 126u : k);
+    if (FIRST) return __float_as_uint(__fmaf_rn(t, (float)KTOP, 8388608.0f));
+    const unsigned k = __float_as_uint(__fmaf_rn(t, (float)(KTOP - 2), 8388609.0f));   // 1 + round((KTOP - 2) t) in the low byte
+    return x < lo ? 0u : (x > hi ? (unsigned)KTOP : k);
 }
 
 template <class Tr, bool FIRST, int DT, int RPT>

@@ -67,6 +67,8 @@ struct W3Geo {
     static constexpr int RT = THREADS / 16;        // rows per trip of the risk sweep (16 lanes share a row)
     static constexpr int NT = W3_ROWS / RT;        // trips
     static constexpr int SLOTS = W3_ROWS;          // keys per column, sentinels included
+    static constexpr int KBITS = 7;                // key bits: keys 0..126, 127 = sentinel
+    static constexpr int NEXT = 2;                 // buckets above the median's searched for the next value
 };
 
 struct W3Ctx {
@@ -177,7 +179,7 @@ __device__ __forceinline__ void sel_build_keys(const typename Tr::in_t *x, const
         for (int b = 0; b < 4; ++b) {
             const int j = 4 * q + b;
             const typename Tr::in_t xv = FROM_REGS ? x[j] : val(j);
-            f[b] = wide_key<Tr, FIRST>(xv, lo, hi, sc);        // pack4 takes the low byte
+            f[b] = wide_key<Tr, FIRST, (1 << G::KBITS) - 2>(xv, lo, hi, sc);        // pack4 takes the low byte
             if (!FULL && val.row(j) >= N) f[b] = 127u;
             if (ONLY_VALID && ((old >> (8 * b)) & 0xffu) == 127u) f[b] = 127u;
         }
@@ -242,7 +244,7 @@ __device__ __forceinline__ typename Tr::val_t sel_centre(const W3Ctx &w, const V
         int L = 0, LE = n_valid;
         const int sum_keys = w3_key_sum(kw);
 #pragma unroll
-        for (int bit = 6; bit >= 0; --bit) {
+        for (int bit = G::KBITS - 1; bit >= 0; --bit) {
             const unsigned cand = prefix | (1u << bit);
             const int ge = sel_col_sum<G>(w, w3_count_ge(kw, cand, sum_keys));
             const int lt = G::SLOTS - ge;        // sentinels (127) are never below a pivot
@@ -266,9 +268,9 @@ __device__ __forceinline__ typename Tr::val_t sel_centre(const W3Ctx &w, const V
         in_t thr = const_value;
         if (khi >= LE) {
             // Rank klo is the LAST of its bucket and rank khi the first value above it: v_lo = the bucket's maximum,
-            // v_hi = the minimum of the next two buckets (w2) — no ranking, no candidate list; an empty w2 (rare)
+            // v_hi = the minimum of the next G::NEXT buckets (w2) — no ranking, no candidate list; an empty w2 (rare)
             // leaves the scan over all valid values above v_lo.
-            const unsigned up = prefix + 3u > 127u ? 127u : prefix + 3u;
+            const unsigned up = prefix + 1u + G::NEXT > 127u ? 127u : prefix + 1u + G::NEXT;
             const unsigned cC = (128u - up) * 0x01010101u;
             unsigned w2[MW] = {};
 #pragma unroll

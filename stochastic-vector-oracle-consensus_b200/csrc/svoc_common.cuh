@@ -46,6 +46,17 @@ __device__ __forceinline__ u64 wmul_sq(i64 diff) {
     return (a * a + (u64)HALF_WSAD) / (u64)WSAD;
 }
 
+// The same for |diff| <= 1 048 999 (constrained inputs: both the value and the centre lie in [0, 1e6]) in 32-bit
+// arithmetic only: with a = 1000 a1 + a0,  a^2 = 1e6 a1^2 + 2000 a1 a0 + a0^2, so
+//     (a^2 + 500000) / 1e6 = a1^2 + (2000 a1 a0 + a0^2 + 500000) / 1e6        (truncating divisions)
+// and the second numerator stays below 2^31 (2000 * 1048 * 999 + 999^2 + 5e5 = 2 095 402 001).  Ten 32-bit
+// instructions instead of a 64-bit multiply and a 64-bit division by a constant; exhaustively checked against the
+// 64-bit form over the whole range in tests/test_host_logic.py.
+__host__ __device__ __forceinline__ uint32_t wmul_sq_small(uint32_t a) {
+    const uint32_t a1 = a / 1000u, a0 = a - a1 * 1000u;
+    return a1 * a1 + (2000u * a1 * a0 + a0 * a0 + 500000u) / 1000000u;
+}
+
 // wsad_div(a, b) = (a*W + b/2) / b with i128 intermediates (signed_decimal.cairo:114-116).
 __device__ __forceinline__ i64 wdiv_wide(i64 a, i64 b) {
     i128 num = (i128)a * (i128)WSAD + (i128)(b / 2);

@@ -158,3 +158,16 @@ def test_wire_format_codecs():
     cd = c.constructor_calldata(["0x1", "0x2", "0x3"], True, 2, 2, True, 0, 6, list(range(10, 17)))
     assert cd == [3, 1, 2, 3, 1, 2, 2, 1, 0, 6, 7, 10, 11, 12, 13, 14, 15, 16]        # contract/README.md:40-66
     assert c.constructor_calldata([5], False, 1, 0, False, -3, 1, [9])[6] == P - 3
+
+
+def test_32_bit_square_reduction_is_exact_over_the_constrained_range():
+    """csrc/svoc_common.cuh wmul_sq_small: wsad_mul(d, d) = (d*d + 500000) / 1000000 (signed_decimal.cairo:110-112,
+    math.cairo:170-173) for |d| <= 1 048 999 with 32-bit intermediates only — the restated formula, checked here
+    against plain 64-bit arithmetic for EVERY value of the range, and the 32-bit bound on its numerator."""
+    a = np.arange(0, 1_049_000, dtype=np.int64)
+    a1, a0 = a // 1000, a % 1000
+    num = 2000 * a1 * a0 + a0 * a0 + 500000
+    assert int(num.max()) < 2**31
+    assert np.array_equal(a1 * a1 + num // 1_000_000, (a * a + 500000) // 1_000_000)
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "stochastic-vector-oracle-consensus_b200", "csrc", "svoc_common.cuh")).read()
+    assert "a1 * a1 + (2000u * a1 * a0 + a0 * a0 + 500000u) / 1000000u" in src      # the formula tested is the one compiled
