@@ -178,10 +178,10 @@ def test_float_bulk_vs_oracle(N, D, F, T, dt):
         r = _np_result(svoc.consensus_float(x, F, centre=centre, tie_rule=tie, want_moments=False, want_qr=False, want_essence=False), N)
         # measured: fp64 differs on no round; fp32 on a few per thousand (risks within 1e-6 of each other at the cut)
         _float_compare(r, ora, N, F, dt, f"{N}x{D} {dt} centre={centre} bench options",
-                       0.9999 if dt == torch.float64 else 0.99, False)
+                       0.9999 if dt == torch.float64 else 0.999, False)
         r = _np_result(svoc.consensus_float(x, F, centre=centre, tie_rule=tie, want_moments=False), N)
         _float_compare(r, ora, N, F, dt, f"{N}x{D} {dt} centre={centre} all outputs",
-                       0.9999 if dt == torch.float64 else 0.99, True)
+                       0.9999 if dt == torch.float64 else 0.999, True)
 
 
 # ------------------------------------------------------------------------------------------ rare statuses
