@@ -12,9 +12,9 @@
 //   * risks: a lane owns two rows and walks their D elements with a per-lane rotation (conflict-free);
 //   * the kept rows come from the single-warp bisection on the risks (w2_select_rows), all-pairs as its fallback;
 //   * the two Newton square roots of a round (math.cairo:271-292, data-dependent trip counts) are NOT run inside the
-//     round — one busy lane would hold 31 idle ones for ~1000 instructions — but collected per CTA (32 rounds) and
+//     round — one busy lane would hold 31 idle ones for ~1000 instructions — but collected per CTA (128 rounds) and
 //     done at the end, one task per lane.
-// A CTA of 8 warps takes 32 consecutive rounds, 8 at a time, each batch staged by one TMA bulk copy.
+// A CTA of 8 warps takes 128 consecutive rounds; every warp stages its own rounds with its own TMA bulk copies.
 // Moments, rank output and mean centres stay with `small<64>`.
 // Reference semantics: see consensus_kernel.cuh (contract.cairo:442-503 etc.).
 #pragma once
@@ -23,7 +23,7 @@
 namespace svoc {
 
 constexpr int MID_WARPS = 8;         // warps (= rounds in flight) per CTA
-constexpr int MID_ITERS = 4;         // batches per CTA
+constexpr int MID_ITERS = 16;        // rounds per warp: 128 rounds per CTA, so the square-root tail has one task per thread
 constexpr int MID_ROUNDS = MID_WARPS * MID_ITERS;
 constexpr int MID_ROWS = 64;
 
