@@ -150,16 +150,22 @@ __device__ __noinline__ typename Tr::val_t sel_exact_centre(const typename Tr::i
     return column_centre_generic<Tr>(gcol, gstride, N, keep, n_valid, kind, false, sk, ku, stw);
 }
 
-// A thread's values in the swizzled tile, by value index j: src0 points at its first row, src1 at its second row of
-// the same group of 8 (E = 2 only; the two differ by one 128-byte line and the change of the swizzled chunk)
+// A thread's values in the swizzled tile, by value index j: a0 is the shared-memory address of its first row, a1 of
+// its second row of the same group of 8 (E = 2 only; the two differ by one 128-byte line and the change of the
+// swizzled chunk).  Explicit ld.shared: through a struct of generic pointers the compiler no longer saw the address
+// space and emitted generic loads (6 % slower).
+__device__ __forceinline__ void lds32(float &v, uint32_t addr) { asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr)); }
+__device__ __forceinline__ void lds32(int32_t &v, uint32_t addr) { asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr)); }
 template <int P, class in_t>
 struct W3Vals {
-    const in_t *src0, *src1;
+    uint32_t a0, a1;
     int part;
     __device__ __forceinline__ in_t operator()(int j) const {
         constexpr int E = W3Geo<P>::E;
-        if (E == 1) return src0[j * 256];
-        return ((j & 1) ? src1 : src0)[(j >> 1) * 256];
+        in_t v;
+        if (E == 1) lds32(v, a0 + (uint32_t)j * 1024u);
+        else lds32(v, ((j & 1) ? a1 : a0) + (uint32_t)(j >> 1) * 1024u);
+        return v;
     }
     __device__ __forceinline__ int row(int j) const { return w3_row<P>(j, part); }
 };
@@ -168,7 +174,7 @@ struct W3Vals {
 // FROM_REGS: the values are passed in x (first build of a round); otherwise they are read from the tile.
 // ONLY_VALID: rows whose current key is the sentinel (dropped / padded) keep it.
 template <class Tr, class G, bool FIRST, bool FULL, bool ONLY_VALID, bool FROM_REGS, class V>
-__device__ __forceinline__ void sel_build_keys(const typename Tr::in_t *x, const V &val, unsigned (&kw)[G::NKW], int N,
+__device__ __forceinline__ void sel_build_keys(const typename Tr::in_t *x, const V val, unsigned (&kw)[G::NKW], int N,
                                                typename Tr::in_t lo, typename Tr::in_t hi,
                                                const typename WideKey<Tr>::Scale &sc) {
 #pragma unroll
@@ -222,7 +228,7 @@ template <> __device__ __forceinline__ int32_t w3_never_less<int32_t>() { return
 // src0 / src1: this thread's rows in the tile (w3_value).  gcol / keep serve only the rare exact fallback, which
 // walks the column in global memory.  lcw: this column's candidate list (W3_LSTRIDE words).
 template <class Tr, class G, bool FULL, class V>
-__device__ __forceinline__ typename Tr::val_t sel_centre(const W3Ctx &w, const V &val, unsigned (&kw)[G::NKW],
+__device__ __forceinline__ typename Tr::val_t sel_centre(const W3Ctx &w, const V val, unsigned (&kw)[G::NKW],
                                                          const typename Tr::in_t *gcol, int gstride, const uint8_t *keep, int n_valid,
                                                         int kind, bool col_const, bool col_fallback,
                                                         typename Tr::in_t const_value, typename Tr::in_t *lcw,
@@ -493,7 +499,7 @@ consensus_wide3_kernel(const Params p, const __grid_constant__ CUtensorMap tmap)
     const int c32 = c & 31;
     const in_t *src0 = tile_s + (c >> 5) * W3_BOX_WORDS + (E * part) * 32 + ((((c32 >> 2) ^ (E * part)) << 2) | (c32 & 3));
     const in_t *src1 = E == 1 ? src0 : tile_s + (c >> 5) * W3_BOX_WORDS + (E * part + 1) * 32 + ((((c32 >> 2) ^ (E * part + 1)) << 2) | (c32 & 3));
-    const W3Vals<P, in_t> val{src0, src1, part};
+    const W3Vals<P, in_t> val{smem_u32(src0), smem_u32(src1), part};
     // this thread's row unit in the risk sweep: 4-column chunk rh of row RT*t + rg (t = 0 .. NT-1); after the shuffle
     // tree the thread holds the total of row RT * (rh >> (4 - log2 NT)) + rg
     const int rh = lane & 15, rg = warp * 2 + (lane >> 4);
@@ -815,7 +821,21 @@ int launch_wide3_p(const Params &p, const Plan &pl, cudaStream_t st) {
     void (*kern)(const Params, const CUtensorMap) = (p.N == W3_ROWS) ? consensus_wide3_kernel<Tr, P, true> : consensus_wide3_kernel<Tr, P, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
-    kern<<<(unsigned)pl.grid, W3Geo<P>::THREADS, pl.smem, st>>>(p, tmap);
+    // Three CTAs of 75 KB only fit an SM with the largest shared-memory carveout; left to its default the driver
+    // sometimes configured less (two resident CTAs, a second wave for the rest of the grid: 14.2 instead of 15.0 M
+    // rounds/s, box by box).  Ask for the carveout, then size the persistent grid by what is really resident.
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute(carveout): ") + cudaGetErrorString(e));
+    int resident = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, kern, W3Geo<P>::THREADS, pl.smem);
+    if (e != cudaSuccess || resident < 1) return fail(std::string("wide3 occupancy query: ") + cudaGetErrorString(e));
+    int sms = 0, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long long grid = pl.grid;
+    const long long fit = 2 * (((long long)sms * resident) / 2);          // whole clusters
+    if (fit >= 2 && grid > fit) grid = fit;
+    kern<<<(unsigned)grid, W3Geo<P>::THREADS, pl.smem, st>>>(p, tmap);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
     count_launch();
