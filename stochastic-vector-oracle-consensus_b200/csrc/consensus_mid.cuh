@@ -367,6 +367,8 @@ int launch_mid_p(const Params &p, const Plan &pl, cudaStream_t st) {
                                                    : (dexact ? consensus_mid_kernel<Tr, P, false, true> : consensus_mid_kernel<Tr, P, false, false>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    // several CTAs per SM are planned: ask for the full shared-memory carveout (the default is not always enough)
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
     kern<<<(unsigned)pl.grid, MID_WARPS * 32, pl.smem, st>>>(p);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));

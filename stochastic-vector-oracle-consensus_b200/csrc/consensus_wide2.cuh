@@ -892,6 +892,8 @@ int launch_wide2(const Params &p, const Plan &pl, cudaStream_t st) {
 #endif
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
     if (e != cudaSuccess) return fail(std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+    // several CTAs per SM are planned: ask for the full shared-memory carveout (the default is not always enough)
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
     kern<<<(unsigned)pl.grid, W2_THREADS, pl.smem, st>>>(p);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
