@@ -228,3 +228,52 @@ def test_shape_panics_and_sqrt_of_one_on_the_gpu():
         x[0, 0, 0] += 1000 * int(round(np.sqrt(N)))          # kept: qr = N over N kept rows -> avg 1
         x[0, 1, 0] += 300000                                  # dropped
         assert both(x, 1)[0] == 6
+
+
+# ------------------------------------------------------------------------------------------ kernel variants
+MID_SHAPES = [(64, 16, 12), (64, 32, 10), (40, 32, 8), (50, 8, 10), (33, 5, 6), (64, 1, 3), (48, 12, 9), (64, 7, 20)]
+
+
+@pytest.mark.parametrize("N,D,F", MID_SHAPES)
+@pytest.mark.parametrize("kind", ["beta", "coarse", "colluders", "tiny", "extreme", "outside"])
+def test_mid_kernel_every_geometry_vs_oracle(N, D, F, kind):
+    """The warp-per-round kernel (32 < N <= 64) in all its geometries — 1, 2 or 4 lanes per column, D equal to or
+    below the lane grid, N = 64 or less — without moments (with them the small<64> kernel runs): bit-exact in fixed
+    point for every input family, fp32 within tolerance, both against oracle/svoc_ref.c."""
+    import svoc
+    from oracle import cref
+    assert svoc.kernel_variant(N, D, torch.int32) == "mid"
+    rng = np.random.default_rng(seed_of("mid", N, D, kind))
+    T = 300
+    x = gen_fixed(kind, rng, T, N, D)
+    ora = cref.fixed_batch(x, F, True, 0, False, nthreads=0)
+    r = result_to_numpy(svoc.consensus_fixed(torch.from_numpy(x.astype(np.int32)).cuda(), F, want_moments=False))
+    assert_fixed_equal(r, ora, T, want_moments=False, label=f"mid {N}x{D} {kind}")
+    if kind == "beta":
+        xf = (x * 1e-6).astype(np.float32)
+        for centre, tie in ((1, 1), (0, 0)):
+            oraf = cref.float_batch(xf.astype(np.float64), F, centre=centre, tie=tie, want_moments=False, nthreads=0)
+            rf = _np_result(svoc.consensus_float(torch.from_numpy(xf).cuda(), F, centre=centre, tie_rule=tie), N)
+            _float_compare(rf, oraf, N, F, torch.float32, f"mid {N}x{D} fp32 centre={centre}", 0.98, True)
+
+
+@pytest.mark.parametrize("N,F", [(256, 51), (200, 40), (130, 26), (65, 13)])
+@pytest.mark.parametrize("kind", ["beta", "coarse", "colluders", "tiny", "extreme", "outside"])
+def test_wide3_kernel_partial_rounds_vs_oracle(N, F, kind):
+    """The cluster kernel (D = 128) with full and partial rounds (N < 256: the landing box reads past the round and
+    the extra rows are masked), every input family, fixed point bit-exact; fp32 on the beta family."""
+    import svoc
+    from oracle import cref
+    D = 128
+    assert svoc.kernel_variant(N, D, torch.int32) == "wide3"
+    rng = np.random.default_rng(seed_of("w3", N, kind))
+    T = 40
+    x = gen_fixed(kind, rng, T, N, D)
+    ora = cref.fixed_batch(x, F, True, 0, False, nthreads=0)
+    r = result_to_numpy(svoc.consensus_fixed(torch.from_numpy(x.astype(np.int32)).cuda(), F, want_moments=False))
+    assert_fixed_equal(r, ora, T, want_moments=False, label=f"wide3 {N}x{D} {kind}")
+    if kind == "beta":
+        xf = (x * 1e-6).astype(np.float32)
+        oraf = cref.float_batch(xf.astype(np.float64), F, want_moments=False, nthreads=0)
+        rf = _np_result(svoc.consensus_float(torch.from_numpy(xf).cuda(), F), N)
+        _float_compare(rf, oraf, N, F, torch.float32, f"wide3 {N}x{D} fp32", 0.95, True)
