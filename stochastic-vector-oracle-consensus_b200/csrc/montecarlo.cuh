@@ -74,13 +74,7 @@ montecarlo_kernel(const Params p, const McParams m) {
             honest_s[w] = rank < F ? 0 : 1;
         }
         __syncthreads();
-        for (int e = tid; e < nr * (int)round_elems; e += nt) {
-            const int r = e / (int)round_elems, rem = e - r * (int)round_elems;
-            const int i = rem / D, d = rem - i * D;
-            const u64 t = (u64)(m.gen.trial_offset + r0 + r);
-            const float x = draw_component(m.gen, honest_s[r * N + i] == 0, (uint32_t)t, (uint32_t)(t >> 32), i, d, k0, k1);
-            tile[e] = convert_out<in_t>(x);
-        }
+        fill_components<in_t, true>(m.gen, honest_s, N, D, nr, m.gen.trial_offset + r0, tile, tid, nt, k0, k1);
         __syncthreads();
         // ---- the consensus round(s)
         consensus_block<Tr, NPAD>(q, tile, r0, nr, r0, c1, qr_s, stw_s, keep_s);

@@ -56,14 +56,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const GenParams p) {
         }
     }
     Out *out = reinterpret_cast<Out *>(p.pred) + (size_t)r0 * N * D;
-    const int per_round = N * D;
-    for (int e = tid; e < nr * per_round; e += nt) {
-        const int r = e / per_round, rem = e - r * per_round;
-        const int i = rem / D, d = rem - i * D;
-        const u64 t = (u64)(p.c.trial_offset + r0 + r);
-        const float x = draw_component(p.c, failing[(size_t)r * N + i] != 0, (uint32_t)t, (uint32_t)(t >> 32), i, d, k0, k1);
-        out[e] = convert_out<Out>(x);
-    }
+    fill_components<Out, false>(p.c, failing, N, D, nr, p.c.trial_offset + r0, out, tid, nt, k0, k1);
 }
 
 }  // namespace svoc
