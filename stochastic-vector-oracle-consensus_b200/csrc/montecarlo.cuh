@@ -79,9 +79,18 @@ montecarlo_kernel(const Params p, const McParams m) {
         // ---- the consensus round(s)
         consensus_block<Tr, NPAD>(q, tile, r0, nr, r0, c1, qr_s, stw_s, keep_s);
         __syncthreads();
-        // ---- centre of the honest rows (restricted_median(oracles, true_oracles), ipynb beta :395), into c1
+        // ---- centre of the honest rows (restricted_median(oracles, true_oracles), ipynb beta :395), into c1.
+        //      Where the reliable set IS the honest set (most rounds) that centre is the consensus just computed —
+        //      the same function of the same rows — and the third sort of every column is skipped.
+        for (int r = tid; r < nr; r += nt) {
+            bool same = true;
+            for (int i = 0; i < N; ++i) same &= keep_s[r * N + i] == honest_s[r * N + i];
+            stw_s[r] = same ? 1 : 0;           // consensus_block is done with its status words
+        }
+        __syncthreads();
         for (int c = tid; c < nr * D; c += nt) {
             const int r = c / D, d = c - r * D;
+            if (stw_s[r]) { c1[c] = cons_s[c]; continue; }
             const in_t *col = tile + (size_t)r * round_elems + d;
             val_t sk, ku;
             int stw = STW_OK;
@@ -107,8 +116,7 @@ montecarlo_kernel(const Params p, const McParams m) {
             atomicAdd(&acc[16 + ba], 1u);
             atomicAdd(&acc[16 + 256 + bb], 1u);
             s_rel1 += a; s_rel2 += b; q_rel1 += a * a; q_rel2 += b * b;
-            bool same = true;
-            for (int i = 0; i < N; ++i) same &= keep_s[r * N + i] == honest_s[r * N + i];
+            const bool same = stw_s[r] != 0;
             double d2 = 0;
             for (int d = 0; d < D; ++d) {
                 double df = (double)cons_s[r * D + d] - (double)c1[r * D + d];

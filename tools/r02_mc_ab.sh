@@ -1,0 +1,10 @@
+#!/bin/bash
+# same-box A/B of the fused Monte-Carlo kernel (config 5, 100M rounds per step) against build/ab/libsvoc_base.so, then the GPU tests
+L=$PWD/stochastic-vector-oracle-consensus_b200/build/ab/libsvoc_base.so
+for rep in 1 2; do
+for which in cur base; do
+  if [ $which = base ]; then export SVOC_LIB=$L; else unset SVOC_LIB; fi
+  timeout 300 python bench.py --workload c5 --rounds 100000000 --steps 3 --warmup 1 --no-cpu --no-secondary 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$which c5', round(d['value']), d['ms_per_step'], d['stats']['identification_success_pct'], d['stats']['true_consensus_reliability_pct'])"
+done; done
+unset SVOC_LIB
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
