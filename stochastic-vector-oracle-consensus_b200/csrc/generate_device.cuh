@@ -161,28 +161,33 @@ __device__ __forceinline__ void fill_components(const svoc_gen_config &c, const 
         if (u < 1.0f - 0.0331f * x2 * x2 || __logf(u) < 0.5f * x2 + d * (1.0f - v + __logf(v))) return d * v;
         return -1.0f;
     };
-    uint32_t e = tid, it = 0, slot = 0, t_lo = 0, t_hi = 0;
-    float da = 0, ca = 0, db = 0, cb = 0, ga = -1.0f, gb = -1.0f;
+    uint32_t e = tid, it = 0, slot = 0, t_lo = 0, t_hi = 0, cur_pi = 0xffffffffu;
+    float da = 0, ca = 0, db = 0, cb = 0, ga = -1.0f, gb = -1.0f, centre = 0;
     bool failing = false;
-    // Moves the lane to its next element that needs a draw (colluding rows are written on the way: mode + shift,
-    // clipped).  Called before the loop and from its accept branch, so the loop body holds the one Philox site —
+    // Moves the lane to its next element that needs a draw (colluding rows are written on the way).  Called before the loop and from its accept branch, so the loop body holds the one Philox site —
     // a "fresh element" flag tested at the loop head let the compiler split the body in two copies, and lanes
     // in different copies no longer ran their trips together.
     auto next_element = [&]() {
         while (e < total) {
             const uint32_t r = by_round(e), rem = e - r * per_round, i = by_dim(rem), d = rem - i * (uint32_t)D;
             const uint32_t pi = d - by_par(d) * (uint32_t)c.n_params;
-            const float a = (float)c.a[pi], b = (float)c.b[pi];
+            if (pi != cur_pi) {
+                // the constants of this law parameter; a thread mostly stays on one dimension (its elements are
+                // nt apart), so the two double -> float conversions and the two rsqrt run once, not per element
+                cur_pi = pi;
+                const float a = (float)c.a[pi], b = (float)c.b[pi];
+                da = a - 1.0f / 3.0f; ca = rsqrtf(9.0f * da); db = b - 1.0f / 3.0f; cb = rsqrtf(9.0f * db);
+                if (colluding) centre = fminf(fmaxf(beta_mode(a, b) + (float)c.shift, 0.0f), 1.0f);
+            }
             failing = (flags[r * N + i] != 0) != FLAG_IS_HONEST;
-            if (failing && colluding) {
-                out[e] = convert_out<Out>(fminf(fmaxf(beta_mode(a, b) + (float)c.shift, 0.0f), 1.0f));
+            if (failing && colluding) {                               // no draw: mode + shift, clipped
+                out[e] = convert_out<Out>(centre);
                 e += nt;
                 continue;
             }
             const u64 t = (u64)(trial0 + r);
             t_lo = (uint32_t)t; t_hi = (uint32_t)(t >> 32);
             slot = rem;                                               // oracle * D + dim
-            da = a - 1.0f / 3.0f; ca = rsqrtf(9.0f * da); db = b - 1.0f / 3.0f; cb = rsqrtf(9.0f * db);
             ga = -1.0f; gb = -1.0f; it = 0;
             return;
         }
