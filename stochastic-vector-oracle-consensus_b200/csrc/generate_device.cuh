@@ -138,7 +138,8 @@ struct UniformDiv {
 // (round, oracle, dim) of an element comes from multiply-high divisions.
 template <class Out, bool FLAG_IS_HONEST>
 __device__ __forceinline__ void fill_components(const svoc_gen_config &c, const uint8_t *flags, int N, int D, int nr,
-                                                i64 trial0, Out *out, int tid, int nt, uint32_t k0, uint32_t k1) {
+                                                i64 trial0, Out *out, int tid, int nt, const PhiloxKeys &rk) {
+    const uint32_t k0 = rk.k[0], k1 = rk.k[1];
     const uint32_t per_round = (uint32_t)N * (uint32_t)D, total = (uint32_t)nr * per_round;
     const UniformDiv by_round(per_round, total), by_dim((uint32_t)D, per_round), by_par((uint32_t)c.n_params, (uint32_t)D);
     bool decoupled = c.law == SVOC_LAW_BETA;
@@ -194,7 +195,7 @@ __device__ __forceinline__ void fill_components(const svoc_gen_config &c, const 
     };
     next_element();
     while (e < total) {
-        const Philox4 r = philox4x32_10(t_lo, t_hi, slot, failing ? 0x80000000u : 0x20000000u + it, k0, k1);
+        const Philox4 r = philox4x32_10(t_lo, t_hi, slot, failing ? 0x80000000u : 0x20000000u + it, rk);
         const float rad = sqrtf(-2.0f * __logf(u01(r.v[0])));
         float sn, cs;
         __sincosf(6.2831853071795864f * u01(r.v[1]), &sn, &cs);
@@ -214,8 +215,8 @@ __device__ __forceinline__ void fill_components(const svoc_gen_config &c, const 
 }
 
 // failing flags of one round: the F smallest position keys (a uniformly random F-subset)
-__device__ __forceinline__ uint32_t position_key(uint32_t t_lo, uint32_t t_hi, int oracle, uint32_t k0, uint32_t k1) {
-    return philox4x32_10(t_lo, t_hi, 0xFFFF0000u + (uint32_t)oracle, 0, k0, k1).v[0];
+__device__ __forceinline__ uint32_t position_key(uint32_t t_lo, uint32_t t_hi, int oracle, const PhiloxKeys &rk) {
+    return philox4x32_10(t_lo, t_hi, 0xFFFF0000u + (uint32_t)oracle, 0, rk).v[0];
 }
 
 }  // namespace svoc

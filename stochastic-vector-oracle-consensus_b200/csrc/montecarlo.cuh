@@ -19,6 +19,7 @@ struct McParams {
     u64 *counts;
     double *sums;
     i64 n_blocks;
+    PhiloxKeys rk;
 };
 
 template <class Tr, int NPAD>
@@ -49,7 +50,6 @@ montecarlo_kernel(const Params p, const McParams m) {
     const int nacc = 16 + 512 + N + 2;
     for (int k = tid; k < nacc; k += nt) acc[k] = 0;
     double s_rel1 = 0, s_rel2 = 0, q_rel1 = 0, q_rel2 = 0, s_dist = 0, q_dist = 0;
-    const uint32_t k0 = (uint32_t)m.gen.seed, k1 = (uint32_t)(m.gen.seed >> 32);
 
     Params q = p;              // outputs of a block go to shared memory
     q.essence1 = nullptr; q.qr = nullptr; q.reliable = nullptr; q.skew = nullptr; q.kurt = nullptr; q.rank = nullptr;
@@ -65,7 +65,7 @@ montecarlo_kernel(const Params p, const McParams m) {
         for (int w = tid; w < nr * N; w += nt) {
             const int r = w / N, i = w - r * N;
             const u64 t = (u64)(m.gen.trial_offset + r0 + r);
-            keys[w] = position_key((uint32_t)t, (uint32_t)(t >> 32), i, k0, k1);
+            keys[w] = position_key((uint32_t)t, (uint32_t)(t >> 32), i, m.rk);
         }
         __syncthreads();
         for (int w = tid; w < nr * N; w += nt) {
@@ -74,7 +74,7 @@ montecarlo_kernel(const Params p, const McParams m) {
             honest_s[w] = rank < F ? 0 : 1;
         }
         __syncthreads();
-        fill_components<in_t, true>(m.gen, honest_s, N, D, nr, m.gen.trial_offset + r0, tile, tid, nt, k0, k1);
+        fill_components<in_t, true>(m.gen, honest_s, N, D, nr, m.gen.trial_offset + r0, tile, tid, nt, m.rk);
         __syncthreads();
         // ---- the consensus round(s)
         consensus_block<Tr, NPAD>(q, tile, r0, nr, r0, c1, qr_s, stw_s, keep_s);

@@ -311,6 +311,7 @@ int montecarlo_device(const svoc_config *cfg, const svoc_gen_config *gen, int64_
     McParams m;
     m.gen = *gen;
     m.gen.dtype = c.dtype;
+    m.rk = philox_round_keys(gen->seed);
     m.counts = reinterpret_cast<u64 *>(counts);
     m.sums = sums;
     m.n_blocks = (T + rb - 1) / rb;

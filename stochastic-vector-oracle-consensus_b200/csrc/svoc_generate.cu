@@ -18,6 +18,7 @@ struct GenParams {
     void *pred;
     uint32_t *honest;
     int rb, words;
+    PhiloxKeys rk;
 };
 
 template <class Out>
@@ -28,13 +29,12 @@ __global__ void __launch_bounds__(256) generate_kernel(const GenParams p) {
     uint8_t *failing = reinterpret_cast<uint8_t *>(sm + (size_t)p.rb * N);  // [rb][N]
     const i64 r0 = (i64)blockIdx.x * p.rb;
     const int nr = (int)min((i64)p.rb, p.T - r0);
-    const uint32_t k0 = (uint32_t)p.c.seed, k1 = (uint32_t)(p.c.seed >> 32);
     const int tid = threadIdx.x, nt = blockDim.x;
 
     for (int w = tid; w < nr * N; w += nt) {
         const int r = w / N, i = w - r * N;
         const u64 t = (u64)(p.c.trial_offset + r0 + r);
-        keys[w] = position_key((uint32_t)t, (uint32_t)(t >> 32), i, k0, k1);
+        keys[w] = position_key((uint32_t)t, (uint32_t)(t >> 32), i, p.rk);
     }
     __syncthreads();
     for (int w = tid; w < nr * N; w += nt) {
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) generate_kernel(const GenParams p) {
         }
     }
     Out *out = reinterpret_cast<Out *>(p.pred) + (size_t)r0 * N * D;
-    fill_components<Out, false>(p.c, failing, N, D, nr, p.c.trial_offset + r0, out, tid, nt, k0, k1);
+    fill_components<Out, false>(p.c, failing, N, D, nr, p.c.trial_offset + r0, out, tid, nt, p.rk);
 }
 
 }  // namespace svoc
@@ -78,6 +78,7 @@ extern "C" int svoc_generate(const svoc_gen_config *cfg, int64_t n_rounds, void 
             return fail("beta / Kumaraswamy parameters must be > 0");
     GenParams p;
     p.c = *cfg;
+    p.rk = philox_round_keys(cfg->seed);
     p.T = n_rounds;
     p.pred = pred;
     p.honest = honest;
