@@ -194,20 +194,33 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
-// The same wait for a barrier that usually completes MUCH later (a tile copy, a peer CTA's data): try_wait takes a
-// suspend-time hint, so the warp sleeps in hardware instead of spinning through issue slots its neighbours could use
-__device__ __forceinline__ void mbar_wait_sleepy(u64 *bar, uint32_t parity) {
+// The same wait for a barrier that usually completes MUCH later (a tile copy, a peer CTA's data): poll with a
+// growing nanosleep in between.  try_wait with a suspend-time hint came back after ~30 ns each time here (ncu opcode
+// histogram of wide3: ~90 SYNCS.TRYWAIT + NANOSLEEP.SYNCS + SYNCS.PHASECHK + BRA per warp and round, a tenth of
+// the issue slots of an issue-bound kernel); a sleeping warp costs no issue slot.
+#ifndef SVOC_WAIT_CAP_NS
+#define SVOC_WAIT_CAP_NS 256u
+#endif
+__device__ __forceinline__ bool mbar_test(u64 *bar, uint32_t parity) {
+    uint32_t ok;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "SWAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
-        "@p bra SDONE_%=;\n"
-        "bra SWAIT_%=;\n"
-        "SDONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity), "r"(20000u)
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
+    return ok != 0u;
+}
+__device__ __forceinline__ void mbar_wait_sleepy(u64 *bar, uint32_t parity) {
+    if (mbar_test(bar, parity)) return;
+    unsigned ns = 32u;
+    do {
+        __nanosleep(ns);
+        ns = ns < SVOC_WAIT_CAP_NS ? 2u * ns : SVOC_WAIT_CAP_NS;
+    } while (!mbar_test(bar, parity));
 }
 __device__ __forceinline__ void mbar_wait(u64 *bar, uint32_t parity) {
     asm volatile(
