@@ -21,3 +21,14 @@ for f in ('c4','reference','c3'):
         print(f, round(d['value']), d.get('roofline',{}).get('frac'), d.get('e2e',{}).get('value'), d.get('cpu_baseline',{}).get('value'))
     except Exception as e: print(f,'n/a',e)
 "
+# generator kernels (final binary): ncu summaries
+prof() { tag=$1; pat=$2; skip=$3; shift 3
+  "$@" > gpurun_out/plain_$tag.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:$pat -s $skip -c 1 -f -o gpurun_out/prof_$tag "$@" > gpurun_out/ncu_$tag.log 2>&1
+  echo "$tag rc=$?"
+  python profiles/summarize.py full gpurun_out/prof_$tag.ncu-rep > gpurun_out/${tag}_full.txt 2>&1
+  python profiles/src_lines.py gpurun_out/prof_$tag.ncu-rep 1 30 > gpurun_out/${tag}_lines.txt 2>&1
+  python profiles/opcode_hist.py gpurun_out/prof_$tag.ncu-rep ${WR:-1} 30 > gpurun_out/${tag}_opcodes.txt 2>&1
+  rm -f gpurun_out/prof_$tag.ncu-rep; }
+B="python bench.py --steps 1 --warmup 3 --no-cpu --no-secondary"
+WR=16777216 prof r02z_montecarlo montecarlo_kernel 3 $B --workload c5 --rounds 16777216
+WR=65536 prof r02z_generate generate_kernel 0 $B --workload c4 --rounds 65536
