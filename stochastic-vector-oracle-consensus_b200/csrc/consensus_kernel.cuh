@@ -149,11 +149,26 @@ __device__ __forceinline__ typename Tr::val_t column_centre_net(const typename T
     using in_t = typename Tr::in_t;
     using val_t = typename Tr::val_t;
     in_t a[NPAD];
+    if (NPAD >= 16 && __isShared(col)) {
+        // the staged tile (the usual case): rows through the shared-memory window, lds_at.  Rows past N re-read
+        // row 0 (an address inside the tile) and become sentinels.  (8-row columns: measured slower, left alone.)
+        const uint32_t base = smem_u32(col), step = (uint32_t)stride * (uint32_t)sizeof(in_t);
+        constexpr int SURE = NPAD / 2 + 1;     // rows every N of this NPAD has (npad_for: NPAD / 2 < N)
 #pragma unroll
-    for (int i = 0; i < NPAD; ++i) {
-        bool ok = i < N;
-        if (ok && keep) ok = keep[i] != 0;
-        a[i] = ok ? col[(size_t)i * stride] : Tr::sentinel();
+        for (int i = 0; i < NPAD; ++i) {
+            bool ok = i < SURE || i < N;
+            in_t v;
+            lds_at(v, base + (ok ? (uint32_t)i : 0u) * step);
+            if (ok && keep) ok = keep[i] != 0;
+            a[i] = ok ? v : Tr::sentinel();
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NPAD; ++i) {
+            bool ok = i < N;
+            if (ok && keep) ok = keep[i] != 0;
+            a[i] = ok ? col[(size_t)i * stride] : Tr::sentinel();
+        }
     }
     val_t c;
     if (kind == SVOC_CENTRE_MEAN) {

@@ -181,6 +181,14 @@ __host__ __device__ __forceinline__ T pick(const T (&a)[N], int k) {
 // ---------------------------------------------------------------- TMA bulk copy (1-D)
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// A load through the 32-bit shared-memory window.  A pointer into a staged tile reaches the kernels' helper
+// functions as a GENERIC pointer: every element then costs a 64-bit address (multiply, carry, two moves) before
+// its LD; with the window address it is one integer multiply-add and an LDS.
+__device__ __forceinline__ void lds_at(float &v, uint32_t addr) { asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr)); }
+__device__ __forceinline__ void lds_at(double &v, uint32_t addr) { asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr)); }
+__device__ __forceinline__ void lds_at(int32_t &v, uint32_t addr) { asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr)); }
+__device__ __forceinline__ void lds_at(i64 &v, uint32_t addr) { asm volatile("ld.shared.s64 %0, [%1];" : "=l"(v) : "r"(addr)); }
+
 __device__ __forceinline__ void mbar_init(u64 *bar, int count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
