@@ -243,3 +243,29 @@ def test_rounds_to_proposal_to_vote_to_replacement():
     c.set_caller("oracle_new")
     c.update_prediction([400000, 300000])
     assert c.n_active_oracles == 1
+
+
+@pytest.mark.parametrize("n,d,f", [(7, 2, 2), (33, 5, 6), (20, 3, 4), (256, 128, 51), (70, 1000, 9), (300, 300, 40)])
+def test_generator_places_every_component_where_its_flags_say(n, d, f):
+    """fill_components (generate_device.cuh) decodes (round, oracle, dim) from the element index with multiply-high
+    divisions inside their exact range and plain divisions outside it (70 x 1000 and 300 x 300 leave it): a wrong
+    decode would put the colluders' constant rows, or the per-dimension parameters, in the wrong place."""
+    import svoc
+    a = [10.0 + 3.0 * (k % 4) for k in range(min(d, 4))]
+    b = [15.0 + 2.0 * (k % 4) for k in range(min(d, 4))]
+    rounds = 6
+    g = svoc.generate(rounds, n, d, f, a=a, b=b, failing="colluding", shift=0.2, seed=11)
+    x, h = g.pred.cpu().numpy().astype(np.float64), g.honest.cpu().numpy()
+    assert x.shape == (rounds, n, d) and np.all(h.sum(axis=1) == n - f)
+    centre = np.array([min(max((a[k % len(a)] - 1) / (a[k % len(a)] + b[k % len(a)] - 2) + 0.2, 0.0), 1.0) for k in range(d)])
+    assert np.allclose(x[~h], np.broadcast_to(centre, x[~h].shape), atol=1e-6)          # colluders: mode + shift per dimension
+    hon = x[h].reshape(-1, d)
+    assert not np.any(np.isclose(hon, centre, atol=1e-9).all(axis=1))
+    # honest components follow THEIR dimension's beta law: the mean per dimension separates the four parameter pairs
+    if hon.shape[0] * (d // len(a)) >= 2000:
+        for k in range(len(a)):
+            m = hon[:, k::len(a)].mean()
+            assert abs(m - a[k] / (a[k] + b[k])) < 0.01, (k, m)
+    # and the same draws come out of a call that starts later (another decomposition into blocks)
+    g2 = svoc.generate(rounds - 2, n, d, f, a=a, b=b, failing="colluding", shift=0.2, seed=11, trial_offset=2)
+    assert torch.equal(g.pred[2:], g2.pred)

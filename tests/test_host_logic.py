@@ -171,3 +171,43 @@ def test_32_bit_square_reduction_is_exact_over_the_constrained_range():
     assert np.array_equal(a1 * a1 + num // 1_000_000, (a * a + 500000) // 1_000_000)
     src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "stochastic-vector-oracle-consensus_b200", "csrc", "svoc_common.cuh")).read()
     assert "a1 * a1 + (2000u * a1 * a0 + a0 * a0 + 500000u) / 1000000u" in src      # the formula tested is the one compiled
+
+
+def test_multiply_high_division_is_exact_inside_its_stated_range():
+    """csrc/generate_device.cuh UniformDiv: q = umulhi(e, floor(2^32 / d) + 1) equals e // d whenever e * d < 2^32
+    (the `exact` flag; outside it the kernel divides).  Checked on every e for small divisors and on the edges of the
+    range for large ones."""
+    rng = np.random.default_rng(5)
+    divisors = list(range(2, 70)) + [127, 128, 255, 256, 257, 1000, 4096, 14, 32768, 65535, 65536] + rng.integers(2, 1 << 16, 200).tolist()
+    for d in divisors:
+        m = (0xFFFFFFFF // d + 1) & 0xFFFFFFFF
+        top = (1 << 32) // d                                  # e * d < 2^32  <=>  e < 2^32 / d
+        if top <= 1 << 20:
+            e = np.arange(0, top, dtype=np.uint64)
+        else:
+            e = np.unique(np.concatenate([np.arange(0, 1 << 16, dtype=np.uint64), rng.integers(0, top, 1 << 16).astype(np.uint64),
+                                          np.arange(max(top - (1 << 12), 0), top, dtype=np.uint64),
+                                          (np.arange(1, min(top // d, 1 << 12), dtype=np.uint64) * d), (np.arange(1, min(top // d, 1 << 12), dtype=np.uint64) * d - 1)]))
+            e = e[e < top]
+        assert np.array_equal((e * np.uint64(m)) >> np.uint64(32), e // np.uint64(d)), d
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "stochastic-vector-oracle-consensus_b200", "csrc", "generate_device.cuh")).read()
+    assert "m(dd > 1u ? 0xffffffffu / dd + 1u : 0u)" in src and "(u64)max_e * dd < 0x100000000ull" in src
+
+
+def test_philox_round_keys_are_the_key_schedule():
+    """csrc/philox.cuh philox_round_keys: round r uses seed + r * (0x9E3779B9, 0xBB67AE85) — the schedule the pinned
+    Python Philox (tests/philox_ref.py, checked against the Random123 known answers) applies inside its loop."""
+    from philox_ref import philox4x32_10
+    seed = 0x0123_4567_89AB_CDEF
+    k0, k1 = seed & 0xFFFFFFFF, seed >> 32
+    keys = [((k0 + r * 0x9E3779B9) & 0xFFFFFFFF, (k1 + r * 0xBB67AE85) & 0xFFFFFFFF) for r in range(10)]
+
+    def with_round_keys(c):
+        c0, c1, c2, c3 = c
+        for a, b in keys:
+            p0, p1 = 0xD2511F53 * c0, 0xCD9E8D57 * c2
+            c0, c1, c2, c3 = (p1 >> 32) ^ c1 ^ a, p1 & 0xFFFFFFFF, (p0 >> 32) ^ c3 ^ b, p0 & 0xFFFFFFFF
+        return (c0, c1, c2, c3)
+
+    for c in [(0, 0, 0, 0), (1, 2, 3, 4), (0xFFFFFFFF, 0x12345678, 0x9ABCDEF0, 0x20000003)]:
+        assert with_round_keys(c) == tuple(philox4x32_10(c, (k0, k1)))
